@@ -1,0 +1,116 @@
+"""Synthetic RobotCar-shaped refinement problems.
+
+Used by bench.py, the tests and the golden-fixture generator; contains no oracle / reference
+code.  Everything is generated with a seeded `torch.Generator` on the requested device, so the
+bench can build 256 x 201 MB of maps directly in HBM, while tests build small CPU copies that
+are fed, bit-identically, to the oracle (upcast to float64, CHW) and to the CUDA path (HWC fp32).
+
+Per query q (seed = base_seed + q):
+  map    F0 ~ U[0,1) of shape (Hf, Wf, C) fp32, 5x5 box blur per channel (zero pad) so gradients
+         carry signal, L2-normalised over C per cell (as s2dhm/network/network.py:172-173 does);
+         Gx, Gy = un-normalised 3x3 Sobel (zero pad) of F times `grad_scale`, fp32; HWC.
+  K      RobotCar rear camera (s2dhm/datasets/dataload_helpers.py:115-118).
+  points Z ~ U(4, 40) m, X/Z and Y/Z ~ U(-1.3, 1.3)  (about 3 % project outside the image),
+         float64; ground-truth pose (I, 0).
+  ref    F at each point's ground-truth cell + N(0, 0.01^2) noise; a fraction `outlier_frac`
+         of the points takes the descriptor of a random other cell instead.
+  init   rotation U(0.2, 1) degrees about a uniform random axis, translation N(0, 0.05^2) m.
+"""
+import math
+from dataclasses import dataclass
+
+import torch
+
+ROBOTCAR_K = ((400.0, 0.0, 508.222931), (0.0, 400.0, 498.187378), (0.0, 0.0, 1.0))
+
+
+@dataclass
+class Scene:
+    F: torch.Tensor      # (Hf, Wf, C) fp32, HWC
+    Gx: torch.Tensor     # (Hf, Wf, C) fp32
+    Gy: torch.Tensor     # (Hf, Wf, C) fp32
+    ref: torch.Tensor    # (N, C) fp32
+    pts3D: torch.Tensor  # (N, 3) fp64
+    K: torch.Tensor      # (3, 3) fp64 (CPU)
+    R0: torch.Tensor     # (3, 3) fp64 (CPU)
+    t0: torch.Tensor     # (3,) fp64 (CPU)
+    im_width: int
+    im_height: int
+
+    def reference_inputs(self):
+        """The same values in the reference's layout: CHW float64 CPU tensors."""
+        chw = lambda m: m.permute(2, 0, 1).contiguous().double().cpu()
+        return dict(pts3D=self.pts3D.cpu(), feature_ref=self.ref.double().cpu(), feature_map_query=chw(self.F),
+                    feature_grad_x=chw(self.Gx), feature_grad_y=chw(self.Gy), K=self.K.clone(),
+                    im_width=self.im_width, im_height=self.im_height, R_init=self.R0.clone(), t_init=self.t0.clone())
+
+
+def _sobel_hwc(F, grad_scale):
+    """Un-normalised 3x3 Sobel, zero padding, on an (Hf, Wf, C) map; returns HWC Gx, Gy."""
+    x = F.permute(2, 0, 1).unsqueeze(1)  # C,1,H,W
+    kx = torch.tensor([[-1.0, 0.0, 1.0], [-2.0, 0.0, 2.0], [-1.0, 0.0, 1.0]], device=F.device, dtype=F.dtype)
+    ky = kx.t().contiguous()
+    k = torch.stack([kx, ky]).unsqueeze(1)  # 2,1,3,3
+    g = torch.nn.functional.conv2d(x, k, padding=1)  # C,2,H,W
+    if grad_scale != 1.0:
+        g = g * grad_scale
+    gx = g[:, 0].permute(1, 2, 0).contiguous()
+    gy = g[:, 1].permute(1, 2, 0).contiguous()
+    return gx, gy
+
+
+def make_map(C, Hf, Wf, gen, device, grad_scale=1.0):
+    f0 = torch.rand((C, Hf, Wf), generator=gen, device=device, dtype=torch.float32)
+    f = torch.nn.functional.avg_pool2d(f0.unsqueeze(0), 5, stride=1, padding=2, count_include_pad=True).squeeze(0)
+    f = f / f.norm(dim=0, keepdim=True).clamp_min(1e-12)
+    F = f.permute(1, 2, 0).contiguous()
+    Gx, Gy = _sobel_hwc(F, grad_scale)
+    return F, Gx, Gy
+
+
+def _rodrigues(axis, angle):
+    k = axis / axis.norm()
+    Kx = torch.tensor([[0.0, -k[2], k[1]], [k[2], 0.0, -k[0]], [-k[1], k[0], 0.0]], dtype=torch.float64)
+    return torch.eye(3, dtype=torch.float64) + math.sin(angle) * Kx + (1.0 - math.cos(angle)) * (Kx @ Kx)
+
+
+def make_scene(q, N, C, Hf=128, Wf=128, im_width=1024, im_height=1024, device="cpu", base_seed=1234,
+               outlier_frac=0.0, grad_scale=1.0, rot_deg=(0.2, 1.0), trans_sigma=0.05, noise_sigma=0.01,
+               K=ROBOTCAR_K, shared_map=None):
+    """Builds query `q`.  `shared_map=(F, Gx, Gy)` reuses an existing map (several queries that
+    view the same image)."""
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(base_seed + q)
+    cgen = torch.Generator(device="cpu")
+    cgen.manual_seed(base_seed + q)
+    if shared_map is None:
+        F, Gx, Gy = make_map(C, Hf, Wf, gen, dev, grad_scale)
+    else:
+        F, Gx, Gy = shared_map
+    Kt = torch.tensor(K, dtype=torch.float64)
+    # points (CPU generator: tiny, keeps fp64 values identical whatever the device)
+    Z = 4.0 + 36.0 * torch.rand(N, generator=cgen, dtype=torch.float64)
+    xz = -1.3 + 2.6 * torch.rand(N, generator=cgen, dtype=torch.float64)
+    yz = -1.3 + 2.6 * torch.rand(N, generator=cgen, dtype=torch.float64)
+    pts = torch.stack([xz * Z, yz * Z, Z], dim=1).contiguous()
+    # ground-truth cells (clamped to the map for the ~3 % that fall outside the image)
+    u = torch.round(Kt[0, 0] * xz + Kt[0, 2]).long() - 1
+    v = torch.round(Kt[1, 1] * yz + Kt[1, 2]).long() - 1
+    col = torch.div(u.clamp(0, im_width - 1) * Wf, im_width, rounding_mode="floor")
+    row = torch.div(v.clamp(0, im_height - 1) * Hf, im_height, rounding_mode="floor")
+    n_out = int(round(outlier_frac * N))
+    if n_out > 0:
+        sel = torch.randperm(N, generator=cgen)[:n_out]
+        row[sel] = torch.randint(0, Hf, (n_out,), generator=cgen)
+        col[sel] = torch.randint(0, Wf, (n_out,), generator=cgen)
+    cell = (row * Wf + col).to(dev)
+    ref = F.reshape(Hf * Wf, C)[cell]
+    ref = (ref + noise_sigma * torch.randn((N, C), generator=gen, device=dev, dtype=torch.float32)).contiguous()
+    # perturbed initial pose
+    axis = torch.randn(3, generator=cgen, dtype=torch.float64)
+    ang = math.radians(rot_deg[0] + (rot_deg[1] - rot_deg[0]) * float(torch.rand(1, generator=cgen, dtype=torch.float64)))
+    R0 = _rodrigues(axis, ang)
+    t0 = trans_sigma * torch.randn(3, generator=cgen, dtype=torch.float64)
+    return Scene(F=F, Gx=Gx, Gy=Gy, ref=ref, pts3D=pts.to(dev), K=Kt, R0=R0, t0=t0, im_width=im_width,
+                 im_height=im_height)
