@@ -1,0 +1,376 @@
+// fmpnp_capi.cu -- the C ABI declared in include/fmpnp.h: context, workspace, argument checks,
+// launch geometry.  No compute happens on the host; without a CUDA device fmpnp_create() fails.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "fmpnp_kernels.cuh"
+
+using namespace fmpnp;
+
+struct fmpnp_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    char err[512] = {0};
+    // device copy of the problem descriptors + pinned staging
+    QueryDev* d_queries = nullptr;
+    QueryDev* h_queries = nullptr;
+    size_t cap_queries = 0;
+    cudaEvent_t staged = nullptr;
+    bool staged_pending = false;
+    // per-CTA scratch
+    double* d_rec = nullptr;
+    uint8_t* d_supp = nullptr;
+    size_t cap_points = 0;
+    unsigned int* d_counter = nullptr;
+    // geometry (overridable through the environment for tuning)
+    int ring_bytes = 96 * 1024;
+    int depth = 2;
+    int ctas_per_sm = 2;
+    int smem_configured = -1;
+    int64_t launches = 0;
+};
+
+namespace {
+
+int fail(fmpnp_ctx* ctx, int code, const char* fmt, ...) {
+    if (ctx) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+#define FMPNP_CUDA(ctx, call)                                                                           \
+    do {                                                                                                \
+        cudaError_t e__ = (call);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return fail((ctx), e__ == cudaErrorMemoryAllocation ? FMPNP_ERR_OUT_OF_MEMORY : FMPNP_ERR_CUDA, \
+                        "%s failed: %s", #call, cudaGetErrorString(e__));                               \
+    } while (0)
+
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    return atoi(v);
+}
+
+int validate_problem(fmpnp_ctx* ctx, const fmpnp_problem& p, int b, bool need_grad) {
+    if (p.N < 0 || p.C < 1 || p.Hf < 1 || p.Wf < 1 || p.im_width < 1 || p.im_height < 1)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: bad sizes N=%d C=%d Hf=%d Wf=%d im=%dx%d", b, p.N, p.C,
+                    p.Hf, p.Wf, p.im_width, p.im_height);
+    if (p.Hf > 32767 || p.Wf > 32767)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: Hf, Wf must be <= 32767 (int16 cell index of the reference)", b);
+    if (!p.F || !p.ref || (p.N > 0 && !p.pts3D))
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: null F / ref / pts3D", b);
+    if (need_grad && (!p.Gx || !p.Gy))
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: null Gx / Gy", b);
+    return FMPNP_SUCCESS;
+}
+
+// copies the descriptors to the device (through pinned staging) and sizes the per-CTA scratch
+int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32_t* n_max_out, cudaStream_t stream) {
+    if ((size_t)B > ctx->cap_queries) {
+        if (ctx->staged_pending) {
+            FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged));
+            ctx->staged_pending = false;
+        }
+        size_t cap = ctx->cap_queries ? ctx->cap_queries : 256;
+        while (cap < (size_t)B) cap *= 2;
+        if (ctx->d_queries) FMPNP_CUDA(ctx, cudaFree(ctx->d_queries));
+        if (ctx->h_queries) FMPNP_CUDA(ctx, cudaFreeHost(ctx->h_queries));
+        ctx->d_queries = nullptr;
+        ctx->h_queries = nullptr;
+        ctx->cap_queries = 0;
+        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_queries, cap * sizeof(QueryDev)));
+        FMPNP_CUDA(ctx, cudaMallocHost(&ctx->h_queries, cap * sizeof(QueryDev)));
+        ctx->cap_queries = cap;
+    }
+    if (ctx->staged_pending) {  // previous call's H2D copy must have left the staging buffer
+        FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged));
+        ctx->staged_pending = false;
+    }
+    int32_t n_max = 1;
+    for (int32_t b = 0; b < B; ++b) {
+        const fmpnp_problem& p = probs[b];
+        QueryDev& q = ctx->h_queries[b];
+        q.F = p.F;
+        q.Gx = p.Gx;
+        q.Gy = p.Gy;
+        q.ref = p.ref;
+        q.pts = p.pts3D;
+        q.active = p.active;
+        memcpy(q.K, p.K, sizeof(q.K));
+        memcpy(q.R0, p.R0, sizeof(q.R0));
+        memcpy(q.t0, p.t0, sizeof(q.t0));
+        q.N = p.N;
+        q.C = p.C;
+        q.Hf = p.Hf;
+        q.Wf = p.Wf;
+        q.im_w = p.im_width;
+        q.im_h = p.im_height;
+        if (p.N > n_max) n_max = p.N;
+    }
+    FMPNP_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries, ctx->h_queries, (size_t)B * sizeof(QueryDev), cudaMemcpyHostToDevice,
+                                    stream));
+    FMPNP_CUDA(ctx, cudaEventRecord(ctx->staged, stream));
+    ctx->staged_pending = true;
+    const size_t need = (size_t)grid * (size_t)n_max;
+    if (need > ctx->cap_points) {
+        if (ctx->d_rec) FMPNP_CUDA(ctx, cudaFree(ctx->d_rec));
+        if (ctx->d_supp) FMPNP_CUDA(ctx, cudaFree(ctx->d_supp));
+        ctx->d_rec = nullptr;
+        ctx->d_supp = nullptr;
+        ctx->cap_points = 0;
+        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_rec, need * kRecDoubles * sizeof(double)));
+        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_supp, need));
+        ctx->cap_points = need;
+    }
+    *n_max_out = n_max;
+    return FMPNP_SUCCESS;
+}
+
+int geometry(fmpnp_ctx* ctx, int32_t B, int* grid, int* ring_bytes, int* depth, int* slot_bytes) {
+    int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
+    if (d < 2) d = 2;
+    if (d > kMaxDepth) d = kMaxDepth;
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 2) per_sm = 2;
+    const int static_b = (int)refine_static_smem_bytes();
+    const int budget = ctx->max_smem_optin - static_b - 1024;
+    if (ring > budget) ring = budget;
+    int slot = (ring / (kConsumerWarps * d)) & ~127;
+    if (slot < 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", ring);
+    ring = slot * kConsumerWarps * d;
+    if (ctx->smem_configured != ring) {
+        FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(ring));
+        ctx->smem_configured = ring;
+    }
+    int g = ctx->sm_count * per_sm;
+    if (g > B) g = B;
+    if (g < 1) g = 1;
+    *grid = g;
+    *ring_bytes = ring;
+    *depth = d;
+    *slot_bytes = slot;
+    return FMPNP_SUCCESS;
+}
+
+void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, int depth, int slot_bytes) {
+    memset(&lp, 0, sizeof(lp));
+    lp.queries = ctx->d_queries;
+    lp.B = B;
+    lp.rec = ctx->d_rec;
+    lp.supp = ctx->d_supp;
+    lp.n_max = n_max;
+    lp.work_counter = ctx->d_counter;
+    lp.depth = depth;
+    lp.slot_bytes = slot_bytes;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fmpnp_version(void) { return FMPNP_VERSION; }
+
+int fmpnp_struct_size(int which) {
+    switch (which) {
+        case 0: return (int)sizeof(fmpnp_problem);
+        case 1: return (int)sizeof(fmpnp_options);
+        case 2: return (int)sizeof(fmpnp_result);
+        case 3: return (int)sizeof(fmpnp_history);
+        default: return -1;
+    }
+}
+
+int fmpnp_create(fmpnp_ctx** out, int device) {
+    if (!out) return FMPNP_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return FMPNP_ERR_NO_DEVICE;
+    if (device < 0 || device >= count) return FMPNP_ERR_INVALID_ARGUMENT;
+    fmpnp_ctx* ctx = new (std::nothrow) fmpnp_ctx();
+    if (!ctx) return FMPNP_ERR_OUT_OF_MEMORY;
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess ||
+        cudaMalloc(&ctx->d_counter, sizeof(unsigned int)) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->staged, cudaEventDisableTiming) != cudaSuccess) {
+        delete ctx;
+        return FMPNP_ERR_CUDA;
+    }
+    ctx->ring_bytes = env_int("FMPNP_RING_KB", 96) * 1024;
+    ctx->depth = env_int("FMPNP_DEPTH", 2);
+    ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 2);
+    *out = ctx;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_destroy(fmpnp_ctx* ctx) {
+    if (!ctx) return FMPNP_SUCCESS;
+    cudaSetDevice(ctx->device);
+    if (ctx->staged_pending) cudaEventSynchronize(ctx->staged);
+    if (ctx->d_queries) cudaFree(ctx->d_queries);
+    if (ctx->h_queries) cudaFreeHost(ctx->h_queries);
+    if (ctx->d_rec) cudaFree(ctx->d_rec);
+    if (ctx->d_supp) cudaFree(ctx->d_supp);
+    if (ctx->d_counter) cudaFree(ctx->d_counter);
+    if (ctx->staged) cudaEventDestroy(ctx->staged);
+    delete ctx;
+    return FMPNP_SUCCESS;
+}
+
+const char* fmpnp_last_error(const fmpnp_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+int64_t fmpnp_launch_count(const fmpnp_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, const fmpnp_options* o,
+                       fmpnp_result* results, const fmpnp_history* hist, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (B == 0) return FMPNP_SUCCESS;
+    if (!probs || !o || !results || B < 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "null argument or B < 0");
+    if (o->n_iters < 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "n_iters < 0");
+    if (o->loss_id < FMPNP_LOSS_SQUARED || o->loss_id > FMPNP_LOSS_BARRON)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "unknown loss id %d", o->loss_id);
+    if (o->n_levels < 0 || o->n_levels > FMPNP_MAX_LEVELS)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "n_levels must be in [0, %d]", FMPNP_MAX_LEVELS);
+    if (o->solver != FMPNP_SOLVER_CHOLESKY && o->solver != FMPNP_SOLVER_LU)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "unknown solver %d", o->solver);
+    for (int32_t b = 0; b < B; ++b) {
+        int rc = validate_problem(ctx, probs[b], b, true);
+        if (rc) return rc;
+        for (int l = 0; l < o->n_levels; ++l)
+            if (o->levels[l][0] < 0 || o->levels[l][1] > probs[b].C || o->levels[l][0] >= o->levels[l][1])
+                return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "level %d = [%d, %d) outside the %d channels of problem %d", l,
+                            o->levels[l][0], o->levels[l][1], probs[b].C, b);
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    int grid, ring, depth, slot;
+    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    if (rc) return rc;
+    int32_t n_max;
+    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    if (rc) return rc;
+    const int levels_eff = o->n_levels > 0 ? o->n_levels : 1;
+    if (hist) {
+        if (hist->cap < levels_eff * (o->n_iters + 1) || hist->n_stride < n_max || !hist->len || !hist->Rs || !hist->ts ||
+            !hist->costs || !hist->points2d || !hist->mask || !hist->kept)
+            return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "history buffers too small or null (cap %d, n_stride %d)", hist->cap,
+                        hist->n_stride);
+    }
+    LaunchParams lp;
+    fill_common(lp, ctx, B, n_max, depth, slot);
+    lp.mode = kModeRefine;
+    lp.n_iters = o->n_iters;
+    lp.loss_id = o->loss_id;
+    lp.alpha = o->barron_alpha;
+    lp.lambda0 = o->lambda0;
+    lp.use_ratio = std::isnan(o->ratio_threshold) ? 0 : 1;
+    lp.ratio_thr = lp.use_ratio ? o->ratio_threshold : 0.0;
+    lp.n_levels = o->n_levels;
+    memcpy(lp.levels, o->levels, sizeof(lp.levels));
+    lp.solver = o->solver;
+    lp.results = results;
+    if (hist) {
+        lp.hist.enabled = 1;
+        lp.hist.cap = hist->cap;
+        lp.hist.n_stride = hist->n_stride;
+        lp.hist.len = hist->len;
+        lp.hist.Rs = hist->Rs;
+        lp.hist.ts = hist->ts;
+        lp.hist.costs = hist->costs;
+        lp.hist.points2d = hist->points2d;
+        lp.hist.mask = hist->mask;
+        lp.hist.kept = hist->kept;
+    }
+    FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, const fmpnp_options* o, double* costs,
+                             int32_t* n_supported, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (B == 0) return FMPNP_SUCCESS;
+    if (!probs || !o || !costs || B < 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "null argument or B < 0");
+    for (int32_t b = 0; b < B; ++b) {
+        int rc = validate_problem(ctx, probs[b], b, false);
+        if (rc) return rc;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    int grid, ring, depth, slot;
+    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    if (rc) return rc;
+    int32_t n_max;
+    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    if (rc) return rc;
+    LaunchParams lp;
+    fill_common(lp, ctx, B, n_max, depth, slot);
+    lp.mode = kModeComputeCost;
+    lp.use_ratio = std::isnan(o->ratio_threshold) ? 0 : 1;
+    lp.ratio_thr = lp.use_ratio ? o->ratio_threshold : 0.0;
+    lp.cost_out = costs;
+    lp.nsup_out = n_supported;
+    FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int32_t loss_id, double barron_alpha,
+                             double threshold, uint8_t* inliers, int32_t n_stride, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (B == 0) return FMPNP_SUCCESS;
+    if (!probs || !inliers || B < 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "null argument or B < 0");
+    if (loss_id < FMPNP_LOSS_SQUARED || loss_id > FMPNP_LOSS_BARRON)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "unknown loss id %d", loss_id);
+    for (int32_t b = 0; b < B; ++b) {
+        int rc = validate_problem(ctx, probs[b], b, false);
+        if (rc) return rc;
+        if (probs[b].N > n_stride) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "n_stride %d < N of problem %d", n_stride, b);
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    int grid, ring, depth, slot;
+    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    if (rc) return rc;
+    int32_t n_max;
+    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    if (rc) return rc;
+    LaunchParams lp;
+    fill_common(lp, ctx, B, n_max, depth, slot);
+    lp.mode = kModeFindInliers;
+    lp.loss_id = loss_id;
+    lp.alpha = barron_alpha;
+    lp.use_ratio = 1;
+    lp.ratio_thr = threshold;
+    lp.inliers_out = inliers;
+    lp.inliers_stride = n_stride;
+    FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_pack_chw_to_hwc(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, float* dst, int32_t C, int32_t Hf,
+                          int32_t Wf, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!src || !dst || C < 1 || Hf < 1 || Wf < 1) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad pack arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, launch_pack_chw_to_hwc(src, src_is_f64, dst, C, Hf, Wf, static_cast<cudaStream_t>(stream_)));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+}  // extern "C"

@@ -1,0 +1,741 @@
+// fmpnp_kernels.cu -- the feature-metric PnP refinement as ONE persistent sm_100a kernel.
+//
+// Replaces sparseFeaturePnP.forward / multilevel_optimization / compute_cost and find_inliers
+// of featurePnP/model.py (reference lines cited inline).  One CTA owns one query at a time and
+// runs its whole Levenberg-Marquardt loop on the device: no host synchronisation, no
+// per-iteration launch, no collective.
+//
+// Per pose evaluation (the only part that touches HBM in bulk):
+//   producer warp   projects 32 points at a time in float64 (bit-exact pixel indices), then 8
+//                   feeder lanes issue TMA bulk copies (cp.async.bulk -> SASS UBLKCP) of the
+//                   channel-contiguous rows F[cell], Gx[cell], Gy[cell], ref[n] into a
+//                   shared-memory ring guarded by mbarriers (one sub-ring per consumer warp);
+//   consumer warps  read the staged rows as float4, accumulate in float64 the per-point
+//                   c = sum e^2, the 2x2 structure tensor S = G^T G and b = G^T e, reduce over
+//                   the channels with warp shuffles and write one 48-byte record per point;
+//   all threads     apply the robust loss / ratio test, contract (S, b) with the 2x6
+//                   projection Jacobian and block-reduce the 6x6 normal equations;
+//   warp 0          solves the damped system (warp-level Cholesky, pivoted-LU fallback),
+//                   applies the se(3) update and runs the accept / reject / damping schedule.
+// The trial evaluation of iteration i doubles as the linearisation of iteration i+1 when the
+// step is accepted, so every LM iteration gathers each map exactly once: 4*N*C*4 bytes.
+//
+// Channel ranges that are not 16-byte aligned (C, slice start or slice length not a multiple
+// of 4) take a generic path with direct coalesced global loads instead of TMA.
+#include <cmath>
+#include <cstdint>
+
+#include "fmpnp_device.cuh"
+#include "fmpnp_kernels.cuh"
+
+namespace fmpnp {
+
+struct __align__(16) Shared {
+    // --- LM state (thread 0 / warp 0 write, everybody reads after a barrier)
+    double R[9], t[3];    // current pose (last accepted)
+    double Rn[9], tn[3];  // trial pose
+    double Rb[9], tb[3];  // best pose
+    double lin[27];       // accepted linearisation: upper triangle of H (21) + g (6)
+    double ev[28];        // last evaluation: H (21), g (6), sum of rho
+    double A[36], b[8];   // solver workspace
+    double red[kWarps][32];
+    double prev_cost, best_cost, lambda, lr, ev_cost, limit, initial_cost;
+    long long gathered;
+    int32_t red_i[kWarps][4];
+    int32_t ev_count, ev_nsup, best_n, has_best, status, flag, hist_len, query, n_evals, initial_set;
+    int32_t level_status[FMPNP_MAX_LEVELS];
+    // --- staging ring
+    uint64_t full[kConsumerWarps * kMaxDepth];
+    uint64_t empty[kConsumerWarps * kMaxDepth];
+    int2 meta[kConsumerWarps * kMaxDepth];
+    int32_t cellbuf[32];
+};
+
+struct RingPos {
+    int32_t pos;     // slot inside the sub-ring
+    uint32_t phase;  // mbarrier phase parity of that slot's current use
+    __device__ __forceinline__ void advance(int depth) {
+        if (++pos == depth) {
+            pos = 0;
+            phase ^= 1u;
+        }
+    }
+};
+
+struct EvalCtx {
+    const QueryDev* q;
+    int32_t c0, Cl;        // channel slice [c0, c0 + Cl)
+    bool aligned;          // TMA path allowed
+    int32_t loss_id;
+    double alpha;
+    int32_t ratio_mode;    // 0 none, 1 on rho (forward / find_inliers), 2 on raw SSD (compute_cost)
+    double thr;
+    double* rec;           // per-point records of this CTA
+    uint8_t* supp;         // per-point support flags of this CTA
+    int32_t* h_px;         // history slices for the entry being evaluated (or null)
+    uint8_t* h_mask;
+    uint8_t* h_kept;
+    uint8_t* inl_out;      // find_inliers output (or null)
+    unsigned char* ring;
+    int32_t depth, slot_bytes;
+};
+
+// ---------------------------------------------------------------------------------------------
+// channel accumulation: c += e^2, Sxx += gx^2, Sxy += gx gy, Syy += gy^2, bx += gx e, by += gy e
+// (model.py:322, 338, 386-405 after the J = G A factorisation)
+// ---------------------------------------------------------------------------------------------
+template <bool GRAD>
+__device__ __forceinline__ void acc1(float f, float r, float gx, float gy, double (&a)[6]) {
+    const double e = __dadd_rn((double)f, -(double)r);
+    a[0] = fma(e, e, a[0]);
+    if (GRAD) {
+        const double dx = (double)gx, dy = (double)gy;
+        a[1] = fma(dx, dx, a[1]);
+        a[2] = fma(dx, dy, a[2]);
+        a[3] = fma(dy, dy, a[3]);
+        a[4] = fma(dx, e, a[4]);
+        a[5] = fma(dy, e, a[5]);
+    }
+}
+
+// staged rows in a slot: GRAD ? [F | Gx | Gy | ref] : [F | ref], each `nvec` float4 long
+template <bool GRAD>
+__device__ __forceinline__ void accum_slot(const unsigned char* slot, int nvec, int lane, double (&a)[6]) {
+    const float4* pF = reinterpret_cast<const float4*>(slot);
+    const float4* pGx = pF + nvec;
+    const float4* pGy = pF + 2 * nvec;
+    const float4* pR = pF + (GRAD ? 3 : 1) * nvec;
+#pragma unroll 2
+    for (int v = lane; v < nvec; v += 32) {
+        const float4 f = pF[v];
+        const float4 r = pR[v];
+        float4 gx = make_float4(0.f, 0.f, 0.f, 0.f), gy = gx;
+        if (GRAD) {
+            gx = pGx[v];
+            gy = pGy[v];
+        }
+        acc1<GRAD>(f.x, r.x, gx.x, gy.x, a);
+        acc1<GRAD>(f.y, r.y, gx.y, gy.y, a);
+        acc1<GRAD>(f.z, r.z, gx.z, gy.z, a);
+        acc1<GRAD>(f.w, r.w, gx.w, gy.w, a);
+    }
+}
+
+template <bool GRAD>
+__device__ __forceinline__ void finish_point(double (&a)[6], int lane, double* rec_n) {
+    constexpr int NV = GRAD ? 6 : 1;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) a[i] = __dadd_rn(a[i], shfl_xor_f64(a[i], off));
+    }
+    if (lane == 0) {
+        double2* o = reinterpret_cast<double2*>(rec_n);
+        o[0] = make_double2(a[0], a[1]);
+        if (GRAD) {
+            o[1] = make_double2(a[2], a[3]);
+            o[2] = make_double2(a[4], a[5]);
+        }
+    }
+}
+
+// projects point n, records support / history, returns the feature-map cell or -1
+__device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const double* R, const double* t, int n) {
+    const QueryDev& q = *c.q;
+    const bool act = (q.active == nullptr) || (q.active[n] != 0);
+    const double x = q.pts[3 * n + 0], y = q.pts[3 * n + 1], z = q.pts[3 * n + 2];
+    const Proj pr = project_point(R, t, q.K, x, y, z, q.im_w, q.im_h);
+    const bool sup = act && pr.supported;
+    c.supp[n] = sup ? 1 : 0;
+    if (c.h_px) {
+        c.h_px[2 * n + 0] = pr.px;
+        c.h_px[2 * n + 1] = pr.py;
+        c.h_mask[n] = sup ? 1 : 0;
+    }
+    return sup ? cell_index(pr.px, pr.py, q.Hf, q.Wf, q.im_w, q.im_h) : -1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Streaming phase: one record per supported point.
+// ---------------------------------------------------------------------------------------------
+template <bool GRAD>
+__device__ void stream_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const QueryDev& q = *c.q;
+    constexpr int ROWS = GRAD ? 4 : 2;
+    const int N = q.N;
+
+    if (c.aligned) {
+        // channels per staged item: whole slice if it fits a slot, else chunks (multiples of 128 when possible)
+        const int chMax = (c.slot_bytes / (ROWS * 4)) & ~3;
+        const int CH = (c.Cl <= chMax) ? c.Cl : (chMax >= 128 ? (chMax & ~127) : chMax);
+        const int nCh = (c.Cl + CH - 1) / CH;
+        if (warp == 0) {
+            // ---------------- producer: float64 projection + TMA issue
+            for (int base = 0; base < N; base += 32) {
+                const int n = base + lane;
+                int cell = -1;
+                if (n < N) cell = project_and_flag(c, R, t, n);
+                sh.cellbuf[lane] = cell;
+                __syncwarp();
+                if (lane < kConsumerWarps) {
+                    for (int j = lane; j < 32; j += kConsumerWarps) {
+                        const int cj = sh.cellbuf[j];
+                        if (cj < 0) continue;
+                        const int nj = base + j;
+                        const float* srcF = q.F + (size_t)cj * q.C + c.c0;
+                        const float* srcGx = GRAD ? q.Gx + (size_t)cj * q.C + c.c0 : nullptr;
+                        const float* srcGy = GRAD ? q.Gy + (size_t)cj * q.C + c.c0 : nullptr;
+                        const float* srcR = q.ref + (size_t)nj * q.C + c.c0;
+                        for (int ch = 0; ch < nCh; ++ch) {
+                            const int off = ch * CH;
+                            const int cnt = min(CH, c.Cl - off);
+                            const uint32_t rowB = (uint32_t)cnt * 4u;
+                            const int slot = lane * c.depth + rp.pos;
+                            mbar_wait(&sh.empty[slot], rp.phase ^ 1u);
+                            sh.meta[slot] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
+                            mbar_arrive_expect_tx(&sh.full[slot], (uint32_t)ROWS * rowB);
+                            unsigned char* dst = c.ring + (size_t)slot * c.slot_bytes;
+                            tma_bulk_g2s(dst, srcF + off, rowB, &sh.full[slot]);
+                            if (GRAD) {
+                                tma_bulk_g2s(dst + rowB, srcGx + off, rowB, &sh.full[slot]);
+                                tma_bulk_g2s(dst + 2 * rowB, srcGy + off, rowB, &sh.full[slot]);
+                            }
+                            tma_bulk_g2s(dst + (ROWS - 1) * rowB, srcR + off, rowB, &sh.full[slot]);
+                            rp.advance(c.depth);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            if (lane < kConsumerWarps) {  // end-of-evaluation sentinel for "my" consumer warp
+                const int slot = lane * c.depth + rp.pos;
+                mbar_wait(&sh.empty[slot], rp.phase ^ 1u);
+                sh.meta[slot] = make_int2(-1, 0);
+                mbar_arrive(&sh.full[slot]);
+                rp.advance(c.depth);
+            }
+        } else {
+            // ---------------- consumers: warp w drains sub-ring w
+            const int w = warp - 1;
+            double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            for (;;) {
+                const int slot = w * c.depth + rp.pos;
+                mbar_wait(&sh.full[slot], rp.phase);
+                const int2 m = sh.meta[slot];
+                rp.advance(c.depth);
+                if (m.x < 0) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sh.empty[slot]);
+                    break;
+                }
+                const int ch = m.y & 0xffff;
+                if (ch == 0) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) a[i] = 0.0;
+                }
+                const int cnt = min(CH, c.Cl - ch * CH);
+                accum_slot<GRAD>(c.ring + (size_t)slot * c.slot_bytes, cnt >> 2, lane, a);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[slot]);  // slot may be refilled
+                if (m.y >> 30) finish_point<GRAD>(a, lane, c.rec + (size_t)m.x * kRecDoubles);
+            }
+        }
+    } else {
+        // ---------------- generic path: every warp projects its own 32 points, loads directly
+        for (int base = warp * 32; base < N; base += kWarps * 32) {
+            const int n = base + lane;
+            int cell = -1;
+            if (n < N) cell = project_and_flag(c, R, t, n);
+            for (int j = 0; j < 32; ++j) {
+                const int cj = __shfl_sync(0xffffffffu, cell, j);
+                if (cj < 0) continue;
+                const int nj = base + j;
+                const float* srcF = q.F + (size_t)cj * q.C + c.c0;
+                const float* srcGx = GRAD ? q.Gx + (size_t)cj * q.C + c.c0 : nullptr;
+                const float* srcGy = GRAD ? q.Gy + (size_t)cj * q.C + c.c0 : nullptr;
+                const float* srcR = q.ref + (size_t)nj * q.C + c.c0;
+                double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                for (int ch = lane; ch < c.Cl; ch += 32) {
+                    const float f = __ldg(srcF + ch), r = __ldg(srcR + ch);
+                    float gx = 0.f, gy = 0.f;
+                    if (GRAD) {
+                        gx = __ldg(srcGx + ch);
+                        gy = __ldg(srcGy + ch);
+                    }
+                    acc1<GRAD>(f, r, gx, gy, a);
+                }
+                finish_point<GRAD>(a, lane, c.rec + (size_t)nj * kRecDoubles);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Deterministic block reductions (fixed tree: lanes by butterfly, warps in index order)
+// ---------------------------------------------------------------------------------------------
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], int32_t (&iv)[2], Shared& sh, double* out, int32_t* iout) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v[i] = __dadd_rn(v[i], shfl_xor_f64(v[i], off));
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) iv[i] += __shfl_xor_sync(0xffffffffu, iv[i], off);
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+        if (lane == i) sh.red[warp][i] = v[i];
+    if (lane == 0) {
+        sh.red_i[warp][0] = iv[0];
+        sh.red_i[warp][1] = iv[1];
+    }
+    __syncthreads();
+    if (warp == 0) {
+        if (lane < NV) {
+            double s = sh.red[0][lane];
+            for (int w = 1; w < kWarps; ++w) s = __dadd_rn(s, sh.red[w][lane]);
+            out[lane] = s;
+        }
+        if (lane < 2) {
+            int32_t s = 0;
+            for (int w = 0; w < kWarps; ++w) s += sh.red_i[w][lane];
+            iout[lane] = s;
+        }
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-point phase: robust loss, ratio test, contraction with the projection Jacobian, block sums.
+// Leaves sh.ev[0..27], sh.ev_count (survivors), sh.ev_nsup (supported) and sh.ev_cost (mean rho).
+// ---------------------------------------------------------------------------------------------
+template <bool GRAD>
+__device__ void reduce_points(const EvalCtx& c, const double* R, const double* t, Shared& sh) {
+    const QueryDev& q = *c.q;
+    const int N = q.N, tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const bool use_ratio = c.ratio_mode != 0;
+
+    if (use_ratio) {
+        // ratio_threshold_feature_errors (model.py:120-129): limit = max |rho| * threshold
+        double m = -INFINITY;
+        int nanf = 0;
+        for (int n = tid; n < N; n += kThreads) {
+            if (!c.supp[n]) continue;
+            const double x = __dmul_rn(0.5, c.rec[(size_t)n * kRecDoubles]);
+            double rho = x, w = 1.0;
+            if (c.ratio_mode == 1) robust_loss(c.loss_id, c.alpha, x, rho, w);
+            const double a = fabs(rho);
+            if (a != a) nanf = 1;
+            m = fmax(m, a);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            m = fmax(m, shfl_xor_f64(m, off));
+            nanf |= __shfl_xor_sync(0xffffffffu, nanf, off);
+        }
+        if (lane == 0) {
+            sh.red[warp][0] = m;
+            sh.red_i[warp][0] = nanf;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double mm = sh.red[0][0];
+            int nf = sh.red_i[0][0];
+            for (int w = 1; w < kWarps; ++w) {
+                mm = fmax(mm, sh.red[w][0]);
+                nf |= sh.red_i[w][0];
+            }
+            sh.limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
+        }
+        __syncthreads();
+    }
+    const double limit = use_ratio ? sh.limit : 0.0;
+
+    double acc[28];
+#pragma unroll
+    for (int i = 0; i < 28; ++i) acc[i] = 0.0;
+    int32_t cnt[2] = {0, 0};  // survivors, supported
+    const double fx = q.K[0], fy = q.K[4];
+    for (int n = tid; n < N; n += kThreads) {
+        const bool sup = c.supp[n] != 0;
+        bool keep = false;
+        if (sup) {
+            ++cnt[1];
+            const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+            const double2 r0 = r[0];
+            const double x = __dmul_rn(0.5, r0.x);  // cost = 0.5 * sum e^2 (model.py:338)
+            double rho = x, w = 1.0;
+            if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
+            keep = !use_ratio || (fabs(rho) < limit);
+            if (keep) {
+                ++cnt[0];
+                acc[27] = __dadd_rn(acc[27], rho);
+                if (GRAD) {
+                    const double2 r1 = r[1], r2 = r[2];
+                    const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2], q.im_w,
+                                                  q.im_h);
+                    contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, r0.y, r1.x, r1.y, r2.x, r2.y, acc);
+                }
+            }
+        }
+        if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
+        if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
+    }
+    int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
+    block_sum<28>(acc, cnt, sh, sh.ev, iout);
+    if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;  // mean; 0/0 = NaN like torch's empty mean
+    __syncthreads();
+}
+
+template <bool GRAD>
+__device__ __forceinline__ void evaluate(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+    stream_points<GRAD>(c, R, t, sh, rp);
+    __syncthreads();
+    reduce_points<GRAD>(c, R, t, sh);
+    if (threadIdx.x == 0) {
+        sh.n_evals += 1;
+        sh.gathered += (long long)sh.ev_nsup * c.Cl * (GRAD ? 4 : 2);
+    }
+}
+
+__device__ __forceinline__ bool slice_aligned(const QueryDev& q, int c0, int Cl, bool grad, int slot_bytes) {
+    uintptr_t bits = reinterpret_cast<uintptr_t>(q.F) | reinterpret_cast<uintptr_t>(q.ref);
+    if (grad) bits |= reinterpret_cast<uintptr_t>(q.Gx) | reinterpret_cast<uintptr_t>(q.Gy);
+    return (bits & 15u) == 0 && (q.C & 3) == 0 && (c0 & 3) == 0 && (Cl & 3) == 0 && slot_bytes >= 64;
+}
+
+__device__ __forceinline__ int tri_index(int i, int j) {  // upper triangle, row-major, i <= j
+    return i * 6 - (i * (i - 1)) / 2 + (j - i);
+}
+
+// optimizer_step (model.py:37-72) + pose update (model.py:416-426) on warp 0.
+// Reads sh.lin / sh.lambda / sh.lr / sh.R / sh.t; writes sh.Rn / sh.tn, sh.flag = 1 on a NaN step.
+__device__ void solve_and_update(Shared& sh, int solver, int lane) {
+    auto build = [&]() {
+        for (int e = lane; e < 36; e += 32) {
+            const int i = e / 6, j = e % 6;
+            double v = sh.lin[i <= j ? tri_index(i, j) : tri_index(j, i)];
+            if (i == j && sh.lambda != 0.0)  // `if lambda_:` D = (diag(H) + 1e-9); H = H + D * lambda_
+                v = __dadd_rn(v, __dmul_rn(__dadd_rn(v, 1e-9), sh.lambda));
+            sh.A[e] = v;
+        }
+        if (lane < 6) sh.b[lane] = sh.lin[21 + lane];
+        __syncwarp();
+    };
+    build();
+    bool ok = false;
+    if (solver == FMPNP_SOLVER_CHOLESKY) ok = warp_cholesky_solve(sh.A, sh.b, lane);
+    if (!ok) {
+        build();
+        warp_lu_solve(sh.A, sh.b, lane);
+    }
+    if (lane == 0) {
+        double delta[6];
+        bool has_nan = false;
+        for (int i = 0; i < 6; ++i) {
+            delta[i] = __dmul_rn(-sh.lr, sh.b[i]);  // delta = -lr * x   (model.py:62)
+            if (delta[i] != delta[i]) has_nan = true;
+        }
+        if (has_nan) {
+            sh.flag = 1;  // model.py:411-413 (intended `break`)
+        } else {
+            double dr[9];
+            so3exp(delta + 3, dr);                               // dw = delta[3:6]
+            compose_pose(dr, delta, sh.R, sh.t, sh.Rn, sh.tn);   // dt = delta[0:3]
+            sh.flag = 0;
+        }
+    }
+}
+
+__device__ __forceinline__ void hist_record(const LaunchParams& p, int qi, int e, const double* R, const double* t,
+                                            double cost) {
+    if (!p.hist.enabled || e >= p.hist.cap) return;
+    const size_t o = (size_t)qi * p.hist.cap + e;
+    for (int i = 0; i < 9; ++i) p.hist.Rs[o * 9 + i] = R[i];
+    for (int i = 0; i < 3; ++i) p.hist.ts[o * 3 + i] = t[i];
+    p.hist.costs[o] = cost;
+}
+
+__device__ __forceinline__ void hist_slices(const LaunchParams& p, int qi, int e, EvalCtx& c) {
+    if (p.hist.enabled && e < p.hist.cap) {
+        const size_t o = ((size_t)qi * p.hist.cap + e) * p.hist.n_stride;
+        c.h_px = p.hist.points2d + 2 * o;
+        c.h_mask = p.hist.mask + o;
+        c.h_kept = p.hist.kept + o;
+    } else {
+        c.h_px = nullptr;
+        c.h_mask = nullptr;
+        c.h_kept = nullptr;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams p) {
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ Shared sh;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid < kConsumerWarps * kMaxDepth) {
+        mbar_init(&sh.full[tid], 1);
+        mbar_init(&sh.empty[tid], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    RingPos rp;
+    rp.pos = 0;
+    rp.phase = 0;
+    double* rec = p.rec + (size_t)blockIdx.x * p.n_max * kRecDoubles;
+    uint8_t* supp = p.supp + (size_t)blockIdx.x * p.n_max;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) sh.query = (int32_t)atomicAdd(p.work_counter, 1u);
+        __syncthreads();
+        const int qi = sh.query;
+        if (qi >= p.B) break;
+        const QueryDev& q = p.queries[qi];
+
+        EvalCtx c;
+        c.q = &q;
+        c.rec = rec;
+        c.supp = supp;
+        c.ring = ring;
+        c.depth = p.depth;
+        c.slot_bytes = p.slot_bytes;
+        c.h_px = nullptr;
+        c.h_mask = nullptr;
+        c.h_kept = nullptr;
+        c.inl_out = nullptr;
+
+        if (tid == 0) {
+            for (int i = 0; i < 9; ++i) sh.R[i] = q.R0[i];
+            for (int i = 0; i < 3; ++i) sh.t[i] = q.t0[i];
+            sh.n_evals = 0;
+            sh.gathered = 0;
+        }
+        __syncthreads();
+
+        if (p.mode == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
+            c.c0 = 0;
+            c.Cl = q.C;
+            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.loss_id = FMPNP_LOSS_SQUARED;
+            c.alpha = 0.0;
+            c.ratio_mode = p.use_ratio ? 2 : 0;
+            c.thr = p.ratio_thr;
+            evaluate<false>(c, sh.R, sh.t, sh, rp);
+            __syncthreads();
+            if (tid == 0) {
+                p.cost_out[qi] = sh.ev_nsup > 0 ? sh.ev_cost : NAN;
+                if (p.nsup_out) p.nsup_out[qi] = sh.ev_nsup;
+            }
+            continue;
+        }
+        if (p.mode == kModeFindInliers) {  // find_inliers (model.py:131-152)
+            c.c0 = 0;
+            c.Cl = q.C;
+            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.loss_id = p.loss_id;
+            c.alpha = p.alpha;
+            c.ratio_mode = 1;
+            c.thr = p.ratio_thr;
+            c.inl_out = p.inliers_out + (size_t)qi * p.inliers_stride;
+            evaluate<false>(c, sh.R, sh.t, sh, rp);
+            continue;
+        }
+
+        // ------------------------------------------------------------------ refine
+        if (tid == 0) {
+            sh.status = FMPNP_STATUS_OK;
+            sh.has_best = 0;
+            sh.best_cost = NAN;
+            sh.best_n = -1;
+            sh.hist_len = 0;
+            sh.initial_set = 0;
+            sh.initial_cost = NAN;
+            for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) sh.level_status[i] = 0;
+        }
+        __syncthreads();
+        bool run_levels = true;
+        if (p.n_levels > 0) {
+            // multilevel_optimization: initial_cost_ = compute_cost(...) on ALL channels (model.py:182)
+            c.c0 = 0;
+            c.Cl = q.C;
+            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.loss_id = FMPNP_LOSS_SQUARED;
+            c.alpha = 0.0;
+            c.ratio_mode = p.use_ratio ? 2 : 0;
+            c.thr = p.ratio_thr;
+            evaluate<false>(c, sh.R, sh.t, sh, rp);
+            __syncthreads();
+            if (sh.ev_nsup == 0) {  // compute_cost is None -> return the initial pose (model.py:183-187)
+                run_levels = false;
+                if (tid == 0) sh.status = FMPNP_STATUS_NO_INITIAL_COST;
+            } else if (tid == 0) {
+                sh.initial_cost = sh.ev_cost;
+                sh.initial_set = 1;
+            }
+            __syncthreads();
+        }
+        const int nlev = p.n_levels > 0 ? p.n_levels : 1;
+        for (int lvl = 0; run_levels && lvl < nlev; ++lvl) {
+            c.c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
+            c.Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
+            c.aligned = slice_aligned(q, c.c0, c.Cl, true, p.slot_bytes);
+            c.loss_id = p.loss_id;
+            c.alpha = p.alpha;
+            c.ratio_mode = p.use_ratio ? 1 : 0;
+            c.thr = p.ratio_thr;
+
+            // ---- i == 0: cost and linearisation at the incoming pose (model.py:303-359)
+            hist_slices(p, qi, sh.hist_len, c);
+            evaluate<true>(c, sh.R, sh.t, sh, rp);
+            __syncthreads();
+            if (sh.ev_nsup == 0) {  // model.py:316-320 -> forward returns the CURRENT pose
+                if (tid == 0) {
+                    sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                    sh.level_status[lvl] = FMPNP_STATUS_EMPTY_SUPPORT;
+                }
+                __syncthreads();
+                continue;
+            }
+            if (tid == 0) {
+                sh.prev_cost = sh.ev_cost;
+                sh.best_cost = sh.ev_cost;
+                sh.best_n = sh.ev_count;
+                sh.has_best = 1;
+                for (int i = 0; i < 9; ++i) sh.Rb[i] = sh.R[i];
+                for (int i = 0; i < 3; ++i) sh.tb[i] = sh.t[i];
+                if (!sh.initial_set) {  // `if self.initial_cost_ is None` (model.py:355-356)
+                    sh.initial_cost = sh.ev_cost;
+                    sh.initial_set = 1;
+                }
+                for (int i = 0; i < 27; ++i) sh.lin[i] = sh.ev[i];
+                sh.lambda = p.lambda0;  // model.py:281
+                sh.lr = 1.0;
+                sh.status = FMPNP_STATUS_OK;
+                sh.flag = 0;
+                hist_record(p, qi, sh.hist_len, sh.R, sh.t, sh.ev_cost);
+                sh.hist_len += 1;
+            }
+            __syncthreads();
+
+            for (int it = 0; it < p.n_iters; ++it) {
+                if (warp == 0) solve_and_update(sh, p.solver, lane);
+                __syncthreads();
+                if (sh.flag == 1) {
+                    if (tid == 0) sh.status = FMPNP_STATUS_NAN_STEP;
+                    break;
+                }
+                // ---- trial pose: cost (model.py:428-462) and, if accepted, the next linearisation
+                hist_slices(p, qi, sh.hist_len, c);
+                evaluate<true>(c, sh.Rn, sh.tn, sh, rp);
+                __syncthreads();
+                if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
+                    if (tid == 0) {
+                        sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                        sh.flag = 2;
+                    }
+                    break;
+                }
+                if (tid == 0) {
+                    const double new_cost = sh.ev_cost;
+                    hist_record(p, qi, sh.hist_len, sh.Rn, sh.tn, new_cost);  // model.py:464-465
+                    sh.hist_len += 1;
+                    const bool worse = new_cost > sh.prev_cost;
+                    {  // model.py:469-470
+                        const double l = __dmul_rn(sh.lambda, worse ? 10.0 : 0.1);
+                        sh.lambda = l < 1e-6 ? 1e-6 : (l > 1e4 ? 1e4 : l);
+                    }
+                    if (worse) {  // model.py:472-476: reject, keep (R, t) and its linearisation
+                        const double l = __dmul_rn(0.1, sh.lr);
+                        sh.lr = l < 1e-3 ? 1e-3 : (l > 1.0 ? 1.0 : l);
+                    } else {  // model.py:477-486: accept
+                        sh.lr = 1.0;
+                        if (new_cost < sh.best_cost) {
+                            for (int i = 0; i < 9; ++i) sh.Rb[i] = sh.Rn[i];
+                            for (int i = 0; i < 3; ++i) sh.tb[i] = sh.tn[i];
+                            sh.best_n = sh.ev_count;
+                            sh.best_cost = new_cost;
+                        }
+                        sh.prev_cost = new_cost;
+                        for (int i = 0; i < 9; ++i) sh.R[i] = sh.Rn[i];
+                        for (int i = 0; i < 3; ++i) sh.t[i] = sh.tn[i];
+                        for (int i = 0; i < 27; ++i) sh.lin[i] = sh.ev[i];
+                    }
+                }
+                __syncthreads();
+            }
+            __syncthreads();
+            if (tid == 0) {
+                if (sh.flag != 2) {  // model.py:491-494: best pose (else: current pose, unchanged)
+                    for (int i = 0; i < 9; ++i) sh.R[i] = sh.Rb[i];
+                    for (int i = 0; i < 3; ++i) sh.t[i] = sh.tb[i];
+                }
+                sh.level_status[lvl] = sh.status;
+                sh.flag = 0;
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            fmpnp_result& r = p.results[qi];
+            for (int i = 0; i < 9; ++i) r.R[i] = sh.R[i];
+            for (int i = 0; i < 3; ++i) r.t[i] = sh.t[i];
+            r.best_cost = sh.best_cost;
+            r.initial_cost = sh.initial_cost;
+            r.best_num_inliers = sh.best_n;
+            r.status = sh.status;
+            r.n_evaluations = sh.n_evals;
+            for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) r.level_status[i] = sh.level_status[i];
+            r.gathered_rows = sh.gathered;
+            if (p.hist.enabled) p.hist.len[qi] = sh.hist_len;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// CHW (float32 / float64) -> HWC float32 pack: a (C) x (Hf*Wf) transpose through shared memory.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void pack_chw_to_hwc_kernel(const T* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+    __shared__ float tile[32][33];
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, p = p0 + threadIdx.x;
+        if (c < C && p < HW) tile[i][threadIdx.x] = (float)src[(size_t)c * HW + p];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int p = p0 + i, c = c0 + threadIdx.x;
+        if (c < C && p < HW) dst[(size_t)p * C + c] = tile[threadIdx.x][i];
+    }
+}
+
+cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, int C, int Hf, int Wf,
+                                   cudaStream_t stream) {
+    const int HW = Hf * Wf;
+    dim3 block(32, 8), grid((HW + 31) / 32, (C + 31) / 32);
+    if (src_is_f64)
+        pack_chw_to_hwc_kernel<double><<<grid, block, 0, stream>>>(static_cast<const double*>(src), dst, C, HW);
+    else
+        pack_chw_to_hwc_kernel<float><<<grid, block, 0, stream>>>(static_cast<const float*>(src), dst, C, HW);
+    return cudaGetLastError();
+}
+
+size_t refine_static_smem_bytes() { return sizeof(Shared); }
+
+cudaError_t refine_set_max_dynamic_smem(int bytes) {
+    return cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream) {
+    refine_kernel<<<grid, kThreads, ring_bytes, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace fmpnp

@@ -1,0 +1,74 @@
+// fmpnp_kernels.cuh -- launch-parameter structs shared by the kernels (fmpnp_kernels.cu) and
+// the C ABI (fmpnp_capi.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/fmpnp.h"
+
+namespace fmpnp {
+
+constexpr int kConsumerWarps = 8;                 // one sub-ring of the shared-memory staging ring each
+constexpr int kWarps = kConsumerWarps + 1;        // + 1 producer warp (projection + TMA issue)
+constexpr int kThreads = kWarps * 32;             // 288
+constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
+constexpr int kMaxDepth = 8;                      // max slots per sub-ring
+
+enum KernelMode { kModeRefine = 0, kModeComputeCost = 1, kModeFindInliers = 2 };
+
+// Device copy of one fmpnp_problem.
+struct QueryDev {
+    const float* F;
+    const float* Gx;
+    const float* Gy;
+    const float* ref;
+    const double* pts;
+    const uint8_t* active;
+    double K[9], R0[9], t0[3];
+    int32_t N, C, Hf, Wf, im_w, im_h;
+};
+
+struct HistoryDev {
+    int32_t enabled, cap, n_stride;
+    int32_t* len;
+    double* Rs;
+    double* ts;
+    double* costs;
+    int32_t* points2d;
+    uint8_t* mask;
+    uint8_t* kept;
+};
+
+struct LaunchParams {
+    const QueryDev* queries;
+    int32_t B;
+    int32_t mode;
+    // options
+    int32_t n_iters, loss_id, use_ratio, n_levels, solver;
+    double alpha, lambda0, ratio_thr;
+    int32_t levels[FMPNP_MAX_LEVELS][2];
+    // outputs
+    fmpnp_result* results;
+    HistoryDev hist;
+    double* cost_out;      // compute_cost mode
+    int32_t* nsup_out;     // compute_cost mode (may be null)
+    uint8_t* inliers_out;  // find_inliers mode
+    int32_t inliers_stride;
+    // per-CTA scratch
+    double* rec;    // [grid][n_max][kRecDoubles]
+    uint8_t* supp;  // [grid][n_max]
+    int32_t n_max;
+    unsigned int* work_counter;
+    // staging ring geometry
+    int32_t depth;       // slots per consumer warp
+    int32_t slot_bytes;  // bytes per slot (multiple of 128)
+};
+
+// Host-side launchers (defined in fmpnp_kernels.cu)
+cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream);
+cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, int C, int Hf, int Wf,
+                                   cudaStream_t stream);
+size_t refine_static_smem_bytes();
+cudaError_t refine_set_max_dynamic_smem(int bytes);
+
+}  // namespace fmpnp

@@ -1,0 +1,330 @@
+"""ctypes binding of include/fmpnp.h.  Marshals pointers only; all compute is in libfmpnp.so."""
+import ctypes as C
+import math
+import os
+import threading
+
+import numpy as np
+import torch
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MAX_LEVELS = 8
+
+LOSS_IDS = {"squared_loss": 0, "huber_loss": 1, "cauchy_loss": 2, "geman_mcclure_loss": 3, "barron_loss": 4}
+STATUS_OK, STATUS_EMPTY_SUPPORT, STATUS_NAN_STEP, STATUS_NO_INITIAL_COST = 0, 1, 2, 3
+SOLVER_CHOLESKY, SOLVER_LU = 0, 1
+
+
+class FmpnpError(RuntimeError):
+    pass
+
+
+# ---------------------------------------------------------------------------------------------
+# struct mirrors (must match include/fmpnp.h)
+# ---------------------------------------------------------------------------------------------
+class CProblem(C.Structure):
+    _fields_ = [("F", C.c_void_p), ("Gx", C.c_void_p), ("Gy", C.c_void_p), ("ref", C.c_void_p),
+                ("pts3D", C.c_void_p), ("active", C.c_void_p), ("K", C.c_double * 9), ("R0", C.c_double * 9),
+                ("t0", C.c_double * 3), ("N", C.c_int32), ("C", C.c_int32), ("Hf", C.c_int32), ("Wf", C.c_int32),
+                ("im_width", C.c_int32), ("im_height", C.c_int32)]
+
+
+class COptions(C.Structure):
+    _fields_ = [("n_iters", C.c_int32), ("loss_id", C.c_int32), ("barron_alpha", C.c_double),
+                ("lambda0", C.c_double), ("ratio_threshold", C.c_double), ("n_levels", C.c_int32),
+                ("levels", (C.c_int32 * 2) * MAX_LEVELS), ("solver", C.c_int32), ("cluster_size", C.c_int32),
+                ("reserved", C.c_int32 * 6)]
+
+
+class CResult(C.Structure):
+    _fields_ = [("R", C.c_double * 9), ("t", C.c_double * 3), ("best_cost", C.c_double),
+                ("initial_cost", C.c_double), ("best_num_inliers", C.c_int32), ("status", C.c_int32),
+                ("n_evaluations", C.c_int32), ("level_status", C.c_int32 * MAX_LEVELS),
+                ("gathered_rows", C.c_int64)]
+
+
+class CHistory(C.Structure):
+    _fields_ = [("cap", C.c_int32), ("n_stride", C.c_int32), ("len", C.c_void_p), ("Rs", C.c_void_p),
+                ("ts", C.c_void_p), ("costs", C.c_void_p), ("points2d", C.c_void_p), ("mask", C.c_void_p),
+                ("kept", C.c_void_p)]
+
+
+RESULT_DTYPE = np.dtype(CResult)
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+def lib_path():
+    return os.environ.get("FMPNP_LIB", os.path.join(_PKG_DIR, "lib", "libfmpnp.so"))
+
+
+def lib():
+    """Loads libfmpnp.so.  Fails loudly: there is no other implementation to fall back to."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            path = lib_path()
+            if not os.path.exists(path):
+                raise FmpnpError("CUDA library %s is missing: build it with `python -c 'import __graft_entry__ as g; "
+                                 "g.build()'` or `make -C featuremetric-pnp_b200/csrc` (no CPU fallback exists)" % path)
+            L = C.CDLL(path)
+            L.fmpnp_version.restype = C.c_int
+            L.fmpnp_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+            L.fmpnp_create.restype = C.c_int
+            L.fmpnp_destroy.argtypes = [C.c_void_p]
+            L.fmpnp_destroy.restype = C.c_int
+            L.fmpnp_last_error.argtypes = [C.c_void_p]
+            L.fmpnp_last_error.restype = C.c_char_p
+            L.fmpnp_launch_count.argtypes = [C.c_void_p]
+            L.fmpnp_launch_count.restype = C.c_int64
+            L.fmpnp_refine_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.POINTER(COptions),
+                                             C.c_void_p, C.POINTER(CHistory), C.c_void_p]
+            L.fmpnp_refine_batch.restype = C.c_int
+            L.fmpnp_compute_cost_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.POINTER(COptions),
+                                                   C.c_void_p, C.c_void_p, C.c_void_p]
+            L.fmpnp_compute_cost_batch.restype = C.c_int
+            L.fmpnp_find_inliers_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.c_int32, C.c_double,
+                                                   C.c_double, C.c_void_p, C.c_int32, C.c_void_p]
+            L.fmpnp_find_inliers_batch.restype = C.c_int
+            L.fmpnp_pack_chw_to_hwc.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+                                                C.c_int32, C.c_void_p]
+            L.fmpnp_pack_chw_to_hwc.restype = C.c_int
+            _lib = L
+    return _lib
+
+
+class Context:
+    """One fmpnp_ctx (workspace + launch geometry) bound to a CUDA device."""
+
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise FmpnpError("no CUDA device: the feature-metric PnP refinement has no CPU fallback")
+        self.device = torch.cuda.current_device() if device is None else torch.device(device).index or 0
+        h = C.c_void_p()
+        rc = lib().fmpnp_create(C.byref(h), int(self.device))
+        if rc != 0:
+            raise FmpnpError("fmpnp_create failed with %d" % rc)
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().fmpnp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc, what):
+        if rc != 0:
+            msg = lib().fmpnp_last_error(self._h)
+            raise FmpnpError("%s failed (%d): %s" % (what, rc, msg.decode() if msg else "?"))
+
+    @property
+    def launches(self):
+        return int(lib().fmpnp_launch_count(self._h))
+
+
+_default_ctx = {}
+
+
+def default_context(device=None):
+    dev = torch.cuda.current_device() if device is None else (torch.device(device).index or 0)
+    if dev not in _default_ctx:
+        _default_ctx[dev] = Context(dev)
+    return _default_ctx[dev]
+
+
+def loss_id_of(loss):
+    """Maps a gin-registered loss (function object, functools.partial of barron_loss, or name) to
+    (loss_id, barron_alpha)."""
+    import functools
+    if isinstance(loss, int):
+        return int(loss), 0.0
+    if isinstance(loss, str):
+        name = loss.lstrip("@")
+        if name in LOSS_IDS:
+            return LOSS_IDS[name], 0.0
+        raise FmpnpError("unknown loss %r" % loss)
+    if isinstance(loss, functools.partial):
+        name = getattr(loss.func, "__name__", "")
+        if name == "barron_loss":
+            alpha = loss.keywords.get("alpha", loss.args[0] if loss.args else None)
+            if alpha is None:
+                raise FmpnpError("barron_loss partial without alpha")
+            return LOSS_IDS["barron_loss"], float(alpha)
+        return loss_id_of(loss.func)
+    alpha = getattr(loss, "fmpnp_barron_alpha", None)
+    if alpha is not None:
+        return LOSS_IDS["barron_loss"], float(alpha)
+    name = getattr(loss, "__name__", None)
+    if name in LOSS_IDS and name != "barron_loss":
+        return LOSS_IDS[name], 0.0
+    raise FmpnpError("loss_fn %r is not one of %s: arbitrary Python losses cannot run inside the CUDA kernel"
+                     % (loss, sorted(LOSS_IDS)))
+
+
+class Problem:
+    """Device-resident inputs of one query (the product's layout: HWC fp32 maps)."""
+
+    def __init__(self, F, Gx, Gy, ref, pts3D, K, R0, t0, im_width, im_height, active=None):
+        self.F, self.Gx, self.Gy, self.ref, self.pts3D, self.active = F, Gx, Gy, ref, pts3D, active
+        self.K = np.asarray(K.cpu() if isinstance(K, torch.Tensor) else K, dtype=np.float64).reshape(9)
+        self.R0 = np.asarray(R0.cpu() if isinstance(R0, torch.Tensor) else R0, dtype=np.float64).reshape(9)
+        self.t0 = np.asarray(t0.cpu() if isinstance(t0, torch.Tensor) else t0, dtype=np.float64).reshape(3)
+        self.im_width, self.im_height = int(im_width), int(im_height)
+        for name, t_, dt in (("F", F, torch.float32), ("Gx", Gx, torch.float32), ("Gy", Gy, torch.float32),
+                             ("ref", ref, torch.float32), ("pts3D", pts3D, torch.float64),
+                             ("active", active, torch.uint8)):
+            if t_ is None:
+                continue
+            if not (isinstance(t_, torch.Tensor) and t_.is_cuda and t_.dtype == dt and t_.is_contiguous()):
+                raise FmpnpError("%s must be a contiguous CUDA %s tensor" % (name, dt))
+        if F.dim() != 3 or ref.dim() != 2 or pts3D.dim() != 2 or pts3D.shape[1] != 3:
+            raise FmpnpError("expected F (Hf, Wf, C), ref (N, C), pts3D (N, 3)")
+        self.Hf, self.Wf, self.C = (int(v) for v in F.shape)
+        self.N = int(pts3D.shape[0])
+        if tuple(ref.shape) != (self.N, self.C):
+            raise FmpnpError("ref shape %s != (N=%d, C=%d)" % (tuple(ref.shape), self.N, self.C))
+        for g in (Gx, Gy):
+            if g is not None and tuple(g.shape) != tuple(F.shape):
+                raise FmpnpError("gradient map shape %s != F shape %s" % (tuple(g.shape), tuple(F.shape)))
+        if active is not None and tuple(active.shape) != (self.N,):
+            raise FmpnpError("active mask must have shape (N,)")
+
+    @classmethod
+    def from_scene(cls, sc, active=None, R0=None, t0=None):
+        return cls(sc.F, sc.Gx, sc.Gy, sc.ref, sc.pts3D, sc.K, sc.R0 if R0 is None else R0,
+                   sc.t0 if t0 is None else t0, sc.im_width, sc.im_height, active=active)
+
+    def fill(self, c):
+        c.F, c.ref, c.pts3D = self.F.data_ptr(), self.ref.data_ptr(), self.pts3D.data_ptr()
+        c.Gx = self.Gx.data_ptr() if self.Gx is not None else None
+        c.Gy = self.Gy.data_ptr() if self.Gy is not None else None
+        c.active = self.active.data_ptr() if self.active is not None else None
+        c.K[:] = self.K.tolist()
+        c.R0[:] = self.R0.tolist()
+        c.t0[:] = self.t0.tolist()
+        c.N, c.C, c.Hf, c.Wf = self.N, self.C, self.Hf, self.Wf
+        c.im_width, c.im_height = self.im_width, self.im_height
+
+
+def _problem_array(problems):
+    arr = (CProblem * len(problems))()
+    for i, p in enumerate(problems):
+        p.fill(arr[i])
+    return arr
+
+
+def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None):
+    o = COptions()
+    lid, alpha = loss_id_of(loss)
+    if barron_alpha is not None:
+        alpha = float(barron_alpha)
+    o.n_iters, o.loss_id, o.barron_alpha = int(n_iters), lid, alpha
+    o.lambda0 = float(lambda_)
+    o.ratio_threshold = float("nan") if ratio_threshold is None else float(ratio_threshold)
+    levels = list(levels) if levels else []
+    if len(levels) > MAX_LEVELS:
+        raise FmpnpError("at most %d pyramid levels" % MAX_LEVELS)
+    o.n_levels = len(levels)
+    for i, lv in enumerate(levels):
+        o.levels[i][0], o.levels[i][1] = int(lv[0]), int(lv[1])
+    o.solver = {"cholesky": SOLVER_CHOLESKY, "lu": SOLVER_LU}[solver] if isinstance(solver, str) else int(solver)
+    return o
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_threshold=None, levels=None,
+                 track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None):
+    """Batched sparseFeaturePnP.forward (levels=None) / multilevel_optimization (levels=[(s, e), ...]).
+
+    Returns a dict: `results` (numpy structured array, one fmpnp_result per query, on the host if
+    sync else None), `results_dev` (raw device tensor), and with track=True `history` (dict of
+    host numpy arrays: len, Rs, ts, costs, points2d, mask, kept)."""
+    ctx = ctx or default_context()
+    B = len(problems)
+    dev = torch.device("cuda", ctx.device)
+    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha)
+    arr = _problem_array(problems)
+    res_dev = out if out is not None else torch.empty((max(B, 1), RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
+    hist, hbuf = None, None
+    if track:
+        cap = max(1, o.n_levels) * (int(n_iters) + 1)
+        n_stride = max([p.N for p in problems] + [1])
+        hbuf = dict(len=torch.zeros(B, dtype=torch.int32, device=dev),
+                    Rs=torch.zeros((B, cap, 3, 3), dtype=torch.float64, device=dev),
+                    ts=torch.zeros((B, cap, 3), dtype=torch.float64, device=dev),
+                    costs=torch.zeros((B, cap), dtype=torch.float64, device=dev),
+                    points2d=torch.zeros((B, cap, n_stride, 2), dtype=torch.int32, device=dev),
+                    mask=torch.zeros((B, cap, n_stride), dtype=torch.uint8, device=dev),
+                    kept=torch.zeros((B, cap, n_stride), dtype=torch.uint8, device=dev))
+        hist = CHistory()
+        hist.cap, hist.n_stride = cap, n_stride
+        for k in ("len", "Rs", "ts", "costs", "points2d", "mask", "kept"):
+            setattr(hist, k, hbuf[k].data_ptr())
+    rc = lib().fmpnp_refine_batch(ctx._h, arr, B, C.byref(o), C.c_void_p(res_dev.data_ptr()),
+                                  C.byref(hist) if hist is not None else None, _stream_ptr())
+    ctx.check(rc, "fmpnp_refine_batch")
+    ret = {"results_dev": res_dev, "results": None}
+    if sync:
+        ret["results"] = res_dev[:B].cpu().numpy().view(RESULT_DTYPE).reshape(B)
+        if track:
+            ret["history"] = {k: v.cpu().numpy() for k, v in hbuf.items()}
+    elif track:
+        ret["history_dev"] = hbuf
+    return ret
+
+
+def compute_cost_batch(problems, ratio_threshold=None, ctx=None):
+    """Batched sparseFeaturePnP.compute_cost at (R0, t0); returns (costs [B] with NaN == None, n_supported [B])."""
+    ctx = ctx or default_context()
+    B = len(problems)
+    dev = torch.device("cuda", ctx.device)
+    o = _options(1, "squared_loss", 0.0, ratio_threshold, None, "cholesky")
+    arr = _problem_array(problems)
+    costs = torch.empty(max(B, 1), dtype=torch.float64, device=dev)
+    nsup = torch.empty(max(B, 1), dtype=torch.int32, device=dev)
+    rc = lib().fmpnp_compute_cost_batch(ctx._h, arr, B, C.byref(o), C.c_void_p(costs.data_ptr()),
+                                        C.c_void_p(nsup.data_ptr()), _stream_ptr())
+    ctx.check(rc, "fmpnp_compute_cost_batch")
+    return costs[:B], nsup[:B]
+
+
+def find_inliers_batch(problems, threshold, loss="squared_loss", barron_alpha=None, ctx=None):
+    """Batched find_inliers at (R0, t0); returns a uint8 device tensor [B][max N]."""
+    ctx = ctx or default_context()
+    B = len(problems)
+    dev = torch.device("cuda", ctx.device)
+    lid, alpha = loss_id_of(loss)
+    if barron_alpha is not None:
+        alpha = float(barron_alpha)
+    if threshold is None or (isinstance(threshold, float) and math.isnan(threshold)):
+        raise FmpnpError("find_inliers needs a threshold")
+    n_stride = max([p.N for p in problems] + [1])
+    arr = _problem_array(problems)
+    out = torch.zeros((max(B, 1), n_stride), dtype=torch.uint8, device=dev)
+    rc = lib().fmpnp_find_inliers_batch(ctx._h, arr, B, lid, alpha, float(threshold), C.c_void_p(out.data_ptr()),
+                                        n_stride, _stream_ptr())
+    ctx.check(rc, "fmpnp_find_inliers_batch")
+    return out[:B]
+
+
+def pack_chw_to_hwc(src, ctx=None):
+    """CHW float32/float64 CUDA tensor (the reference's layout) -> HWC float32 (the kernel's layout)."""
+    ctx = ctx or default_context()
+    if not (isinstance(src, torch.Tensor) and src.is_cuda and src.dim() == 3 and src.is_contiguous()
+            and src.dtype in (torch.float32, torch.float64)):
+        raise FmpnpError("pack_chw_to_hwc expects a contiguous CUDA float32/float64 (C, Hf, Wf) tensor")
+    Cn, Hf, Wf = (int(v) for v in src.shape)
+    dst = torch.empty((Hf, Wf, Cn), dtype=torch.float32, device=src.device)
+    rc = lib().fmpnp_pack_chw_to_hwc(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
+                                     C.c_void_p(dst.data_ptr()), Cn, Hf, Wf, _stream_ptr())
+    ctx.check(rc, "fmpnp_pack_chw_to_hwc")
+    return dst

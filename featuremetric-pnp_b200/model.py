@@ -1,0 +1,213 @@
+"""Drop-in for the reference's `featurePnP/model.py`: same module name, same gin-configurable
+`sparseFeaturePnP` constructor and call signatures, same returned poses, attributes and `track_`
+history -- but the whole Levenberg-Marquardt loop runs in ONE hand-written sm_100a CUDA kernel
+(libfmpnp.so, reached through the C ABI of include/fmpnp.h).
+
+Usage is unchanged for the reference's callers (s2dhm/pose_prediction/optimize_feature_pnp.py:17):
+
+    sys.path.append('featuremetric-pnp_b200/')      # instead of 'featurePnP/'
+    from model import sparseFeaturePnP, find_inliers
+
+Differences that are deliberate and documented in DESIGN.md:
+  * inputs may live on any device / float dtype; they are moved to the GPU once, packed to
+    channel-contiguous HWC float32 (cached per source tensor) and the arithmetic is float64.
+    The reference's callers feed float32-representable maps (`hypercolumn.type(DoubleTensor)`);
+  * `useGPU` is accepted and ignored: there is no CPU path (a missing CUDA device raises);
+  * a NaN step leaves the loop and returns the best pose -- the reference's intended behaviour
+    (its `logging.warning` at model.py:412 is a NameError because `logging` is never imported);
+  * `loss_fn` must be one of the gin-registered losses (or barron_loss with an alpha).
+"""
+from __future__ import division, print_function
+
+import collections
+
+import numpy as np
+import torch
+from torch import nn
+
+try:
+    import gin
+except ImportError:  # pragma: no cover
+    from helpers import _gin_shim as gin
+
+import fmpnp_b200 as _fm
+from helpers.utils import (barron_loss, cauchy_loss, geman_mcclure_loss, huber_loss, scaled_loss,  # noqa: F401
+                           sobel_filter, squared_loss)
+
+# ------------------------------------------------------------------------------------------------
+# packing cache: CHW (reference layout) -> HWC fp32 on the device, keyed by the source tensor
+# ------------------------------------------------------------------------------------------------
+_PACK_CACHE = collections.OrderedDict()
+_PACK_CACHE_MAX = 8
+
+
+def _device():
+    if not torch.cuda.is_available():
+        raise _fm.FmpnpError("sparseFeaturePnP needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _pack_map(m):
+    """(C, Hf, Wf) tensor, any device / float dtype -> contiguous CUDA HWC float32."""
+    if m.dim() != 3:
+        raise ValueError("feature maps must be (C, Hf, Wf); got %s" % (tuple(m.shape),))
+    key = (m.data_ptr(), tuple(m.shape), tuple(m.stride()), m.dtype, str(m.device), m._version)
+    hit = _PACK_CACHE.get(key)
+    if hit is not None:
+        _PACK_CACHE.move_to_end(key)
+        return hit[1]
+    src = m
+    if src.dtype not in (torch.float32, torch.float64):
+        src = src.double()
+    src = src.to(_device(), non_blocking=True).contiguous()
+    out = _fm.pack_chw_to_hwc(src)
+    _PACK_CACHE[key] = (m, out)  # keeping `m` alive keeps data_ptr unique
+    while len(_PACK_CACHE) > _PACK_CACHE_MAX:
+        _PACK_CACHE.popitem(last=False)
+    return out
+
+
+def clear_pack_cache():
+    _PACK_CACHE.clear()
+
+
+def _dev_tensor(x, dtype):
+    return torch.as_tensor(x).to(device=_device(), dtype=dtype).contiguous()
+
+
+def _problem(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height, R, t,
+             c_range=None):
+    F = _pack_map(feature_map_query)
+    Gx = _pack_map(feature_grad_x) if feature_grad_x is not None else None
+    Gy = _pack_map(feature_grad_y) if feature_grad_y is not None else None
+    ref = _dev_tensor(feature_ref, torch.float32)
+    if ref.dim() == 1:
+        ref = ref[:, None].contiguous()
+    pts = _dev_tensor(pts3D, torch.float64).reshape(-1, 3)
+    if c_range is not None:  # a channel slice of the descriptors was passed against full maps
+        raise ValueError("internal: c_range is handled through pyramid levels")
+    return _fm.Problem(F, Gx, Gy, ref, pts, torch.as_tensor(K).double().cpu(), torch.as_tensor(R).double().cpu(),
+                       torch.as_tensor(t).double().cpu(), int(im_width), int(im_height))
+
+
+@gin.configurable
+def find_inliers(pts3D, R, t, feature_map_query, feature_ref, K, im_width, im_height, threshold=None,
+                 loss_fn=squared_loss, mode="ratio_max"):
+    """Boolean mask over all points: projected inside the image AND robust cost below
+    threshold * max robust cost (reference model.py:131-152).  Any mode other than "ratio_max"
+    returns None, as in the reference."""
+    if mode != "ratio_max":
+        return None
+    prob = _problem(pts3D, feature_ref, feature_map_query, None, None, K, im_width, im_height, R, t)
+    out = _fm.find_inliers_batch([prob], threshold, loss=loss_fn)
+    return out[0, :prob.N].bool().cpu()
+
+
+@gin.configurable
+class sparseFeaturePnP(nn.Module):
+    def __init__(self, n_iters, loss_fn=squared_loss, lambda_=0.01, verbose=False, ratio_threshold=None,
+                 useGPU=False):
+        super().__init__()
+        self.iterations = n_iters
+        self.loss_fn = loss_fn
+        self.verbose = verbose
+        self.lambda_ = lambda_
+        self.track_ = {"Rs": [], "ts": [], "costs": [], "points2d": [], "mask": [], "threshold_mask": []}
+        self.use_ratio_test_ = ratio_threshold is not None
+        self.ratio_threshold_ = ratio_threshold
+        self.initial_cost_ = None
+        self.useGPU = useGPU  # accepted for compatibility; the optimizer always runs on the GPU
+        self.solver = "cholesky"
+        _fm.loss_id_of(loss_fn)  # fail early on a loss the kernel cannot evaluate
+
+    def track(self, R, t, cost, points_2d, mask, threshold_mask):
+        self.track_["Rs"].append(R)
+        self.track_["ts"].append(t)
+        self.track_["costs"].append(cost)
+        self.track_["points2d"].append(points_2d)
+        self.track_["mask"].append(mask)
+        self.track_["threshold_mask"].append(threshold_mask)
+
+    # -- shared tail of forward / multilevel_optimization ---------------------------------------
+    def _run(self, prob, levels, track):
+        out = _fm.refine_batch([prob], self.iterations, loss=self.loss_fn, lambda_=self.lambda_,
+                               ratio_threshold=self.ratio_threshold_, levels=levels, track=bool(track),
+                               solver=self.solver)
+        r = out["results"][0]
+        if track:
+            h = out["history"]
+            n = int(h["len"][0])
+            N = prob.N
+            for e in range(n):
+                m = torch.from_numpy(h["mask"][0, e, :N].astype(bool))
+                thr = None
+                if self.use_ratio_test_:
+                    thr = torch.from_numpy(h["kept"][0, e, :N].astype(bool))[m]
+                self.track(torch.from_numpy(h["Rs"][0, e].copy()), torch.from_numpy(h["ts"][0, e].copy()),
+                           float(h["costs"][0, e]), torch.from_numpy(h["points2d"][0, e, :N].copy()), m, thr)
+            if self.verbose:
+                for e in range(n):
+                    print("entry", e, float(h["costs"][0, e]))
+        if int(r["best_num_inliers"]) >= 0:  # some level reached its i == 0 block
+            self.best_cost_ = torch.tensor(float(r["best_cost"]), dtype=torch.float64)
+            self.best_num_inliers_ = int(r["best_num_inliers"])
+        self.last_status_ = int(r["status"])
+        R = torch.from_numpy(np.array(r["R"], dtype=np.float64).reshape(3, 3).copy())
+        t = torch.from_numpy(np.array(r["t"], dtype=np.float64).copy())
+        return R, t, r
+
+    @gin.configurable
+    def multilevel_optimization(self, feature_pyramid, pts3D, feature_ref, feature_map_query, feature_grad_x,
+                                feature_grad_y, *args, **kwargs):
+        """Coarse-to-fine refinement over channel slices (reference model.py:179-213).
+        args = (K, im_width, im_height); kwargs carry R_init, t_init and optionally track."""
+        K, im_width, im_height = args[0], args[1], args[2]
+        R_init, t_init = kwargs["R_init"], kwargs["t_init"]
+        track = kwargs.get("track", False)
+        if feature_pyramid is None:
+            self.initial_cost_ = self.compute_cost(pts3D, R_init, t_init, feature_map_query, feature_ref, K, im_width,
+                                                   im_height)
+            if self.initial_cost_ is None:
+                return R_init, t_init
+            return self.forward(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width,
+                                im_height, R_init=R_init, t_init=t_init, track=track)
+        levels = []
+        for start, end, target_size, kernel_size in feature_pyramid:
+            if target_size is not None or kernel_size is not None:
+                raise NotImplementedError(
+                    "pyramid levels with target_size / kernel_size (resize / blur, reference model.py:196-207) are "
+                    "not built yet: no shipped config uses them and their kornia 0.2.2 kernels cannot be pinned")
+            levels.append((int(start), int(end)))
+        prob = _problem(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height,
+                        R_init, t_init)
+        R, t, r = self._run(prob, levels, track)
+        if int(r["status"]) == _fm.STATUS_NO_INITIAL_COST:
+            self.initial_cost_ = None
+            return R_init, t_init
+        self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
+        return R, t
+
+    def compute_cost(self, pts3D, R, t, feature_map_query, feature_ref, K, im_width, im_height):
+        """Mean of 0.5 * ||F[cell] - ref||^2 over the supported points (after the raw-SSD ratio
+        test when ratio_threshold is set); None when no point is supported (reference
+        model.py:216-243)."""
+        prob = _problem(pts3D, feature_ref, feature_map_query, None, None, K, im_width, im_height, R, t)
+        costs, nsup = _fm.compute_cost_batch([prob], ratio_threshold=self.ratio_threshold_)
+        if int(nsup[0].item()) == 0:
+            return None
+        return costs[0].cpu()
+
+    @gin.configurable
+    def forward(self, pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height,
+                R_init=None, t_init=None, track=False, confidence=None, scale=None):
+        """Refines (R, t); returns the best pose as CPU float64 tensors (reference model.py:246-494).
+        `confidence` and `scale` are accepted and ignored, as in the reference."""
+        pts3D = torch.as_tensor(pts3D)
+        R = torch.eye(3, dtype=torch.float64) if R_init is None else R_init
+        t = torch.tensor([1.0, 1.0, 0.0], dtype=torch.float64) if t_init is None else t_init
+        prob = _problem(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height,
+                        R, t)
+        R_out, t_out, r = self._run(prob, None, track)
+        if self.initial_cost_ is None and int(r["best_num_inliers"]) >= 0:
+            self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
+        return R_out, t_out

@@ -1,0 +1,68 @@
+"""CPU: the C-ABI library loads without a GPU and exports every symbol include/fmpnp.h declares;
+struct mirrors in the Python binding have the C sizes; the product fails loudly without CUDA."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ensure_built():
+    import __graft_entry__ as g
+    import fmpnp_b200 as fm
+    if not os.path.exists(fm.lib_path()):
+        g.build()
+    return fm
+
+
+def test_library_exports_every_declared_symbol():
+    fm = _ensure_built()
+    hdr = open(os.path.join(ROOT, "include", "fmpnp.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(fmpnp_[a-z_]+)\s*\(", hdr))
+    assert {"fmpnp_create", "fmpnp_destroy", "fmpnp_refine_batch", "fmpnp_compute_cost_batch",
+            "fmpnp_find_inliers_batch", "fmpnp_pack_chw_to_hwc", "fmpnp_last_error", "fmpnp_version",
+            "fmpnp_launch_count", "fmpnp_struct_size"} <= names
+    L = ctypes.CDLL(fm.lib_path())
+    for n in names:
+        assert hasattr(L, n), "libfmpnp.so does not export " + n
+    assert fm.lib().fmpnp_version() == 100
+
+
+def test_struct_sizes_match_the_c_abi():
+    fm = _ensure_built()
+    from fmpnp_b200 import binding as b
+    L = fm.lib()
+    L.fmpnp_struct_size.restype = ctypes.c_int
+    for which, cls in enumerate((b.CProblem, b.COptions, b.CResult, b.CHistory)):
+        assert L.fmpnp_struct_size(which) == ctypes.sizeof(cls), cls.__name__
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    fm = _ensure_built()
+    h = ctypes.c_void_p()
+    assert fm.lib().fmpnp_create(ctypes.byref(h), 0) != 0  # FMPNP_ERR_NO_DEVICE
+    with pytest.raises(fm.FmpnpError):
+        fm.Context()
+    import model
+    m = model.sparseFeaturePnP(n_iters=1)
+    with pytest.raises(fm.FmpnpError):
+        m(torch.zeros(4, 3, dtype=torch.float64), torch.zeros(4, 2), torch.zeros(2, 8, 8), torch.zeros(2, 8, 8),
+          torch.zeros(2, 8, 8), torch.eye(3, dtype=torch.float64), 64, 64)
+
+
+def test_loss_mapping():
+    fm = _ensure_built()
+    import functools
+    import helpers.utils as hu
+    assert fm.loss_id_of(hu.squared_loss) == (0, 0.0)
+    assert fm.loss_id_of(hu.huber_loss) == (1, 0.0)
+    assert fm.loss_id_of(hu.cauchy_loss) == (2, 0.0)
+    assert fm.loss_id_of(hu.geman_mcclure_loss) == (3, 0.0)
+    assert fm.loss_id_of(functools.partial(hu.barron_loss, alpha=-1.0)) == (4, -1.0)
+    with pytest.raises(fm.FmpnpError):
+        fm.loss_id_of(lambda x: x)
