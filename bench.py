@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py -- refined queries / second of the feature-metric PnP hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): per GPU, 256 synthetic
+RobotCar-shaped queries x 4096 points, C = 1024 hypercolumn channels, 128 x 128 maps
+(F, Gx, Gy HWC fp32 = 201 MB per query, 51.5 GB per GPU: far larger than L2), 1024 x 1024
+image, Gauss-Newton (lambda_ = 0) with squared loss, ratio_threshold = 0.8 and an initial inlier
+mask from find_inliers(threshold = 0.8), 20 LM iterations.
+
+One step = one pass of the hot path over the batch: find_inliers kernel + refinement kernel
+(+ the final result all-gather when N > 1).  `value` has the inputs resident in HBM; `e2e` goes
+through the same C ABI with HOST (pinned) buffers, H2D and D2H inside the timed region.
+Weak scaling: every rank owns its own 256 queries and their maps; no data-path collective.
+
+`--impl reference` times the reference algorithm's CPU port (oracle/, float64, CHW maps, the
+reference's own operation order) on the host cores -- the Python reference itself cannot travel
+to the GPU box (it lives in /root/reference of the build container).
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "featuremetric-pnp_b200"))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "refined queries/sec (20 LM iters, 4k pts, C=1024)"
+UNIT = "queries/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    # workload overrides (exploration only; the defaults are the contract)
+    ap.add_argument("--queries", type=int, default=256, help="queries per GPU")
+    ap.add_argument("--points", type=int, default=4096)
+    ap.add_argument("--channels", type=int, default=1024)
+    ap.add_argument("--map", type=int, default=128)
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--config", default="gn_inlier", choices=["gn_inlier", "geman_lm", "pyramid"])
+    ap.add_argument("--e2e-queries", type=int, default=32, help="queries per e2e step (host-resident inputs)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
+    return ap.parse_args()
+
+
+def workload(args):
+    c = dict(workload="cfg2: synthetic RobotCar-shaped batch, %d queries x %d points per GPU, C=%d, %dx%d maps, "
+             "GN + inlier mask" % (args.queries, args.points, args.channels, args.map, args.map),
+             queries_per_gpu=args.queries, points=args.points, channels=args.channels, map=[args.map, args.map],
+             image=[1024, 1024], n_iters=args.iters, storage="HWC fp32", arithmetic="f64",
+             l2="inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed" % (
+                 args.queries * (3 * args.map * args.map + args.points) * args.channels * 4 / 1e9))
+    if args.config == "gn_inlier":
+        c.update(loss="squared_loss", lambda_=0.0, ratio_threshold=0.8, inlier_mask="find_inliers(threshold=0.8)",
+                 levels=None)
+    elif args.config == "geman_lm":
+        c.update(workload=c["workload"].replace("cfg2", "cfg3").replace("GN + inlier mask", "Geman-McClure LM"),
+                 loss="geman_mcclure_loss", lambda_=0.01, ratio_threshold=None, inlier_mask=None, levels=None)
+    else:
+        C = args.channels
+        c.update(workload=c["workload"].replace("cfg2", "cfg4").replace("GN + inlier mask", "3-level pyramid"),
+                 loss="squared_loss", lambda_=0.01, ratio_threshold=None, inlier_mask=None,
+                 levels=[[C // 2, C], [C // 8, C // 2], [0, C // 8]])
+    return c
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks sampler (NVML), runs during the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, device_index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = torch.cuda.get_device_properties(device_index).uuid
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                fn = getattr(self.nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                    self.nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                bits = int(fn(self.h))
+                for b, n in self.REASONS.items():
+                    if bits & b and n != "gpu_idle":
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (reference algorithm, float64, CHW) on host threads
+# ---------------------------------------------------------------------------------------------
+def scene_to_reference_problem(sc):
+    inp = sc.reference_inputs()
+    return dict(pts3D=inp["pts3D"].numpy(), feature_ref=inp["feature_ref"].numpy(), F=inp["feature_map_query"].numpy(),
+                Gx=inp["feature_grad_x"].numpy(), Gy=inp["feature_grad_y"].numpy(), K=inp["K"].numpy(),
+                im_width=sc.im_width, im_height=sc.im_height), inp["R_init"].numpy(), inp["t_init"].numpy()
+
+
+def cpu_sample(args, cfg, n_queries, threads, scenes=None):
+    """Times `n_queries` full-shape queries with `threads` host threads; returns (queries/s, seconds).
+    `scenes`: reuse the (device-resident) scenes the GPU arm just processed."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle
+    from fmpnp_b200 import synth
+    probs, R0s, t0s = [], [], []
+    for q in range(n_queries):
+        if scenes is not None:
+            sc = scenes[q]
+        else:
+            sc = synth.make_scene(q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device="cpu")
+        p, R0, t0 = scene_to_reference_problem(sc)
+        if cfg["inlier_mask"]:
+            inl = oracle.find_inliers(p["pts3D"], R0, t0, p["F"], p["feature_ref"], p["K"], p["im_width"], p["im_height"],
+                                      0.8, loss=cfg["loss"])
+            p["pts3D"] = np.ascontiguousarray(p["pts3D"][inl])
+            p["feature_ref"] = np.ascontiguousarray(p["feature_ref"][inl])
+        probs.append(p)
+        R0s.append(R0)
+        t0s.append(t0)
+        del sc
+    t = time.perf_counter()
+    oracle.forward_batch(probs, np.stack(R0s), np.stack(t0s), cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                         ratio_threshold=cfg["ratio_threshold"], levels=cfg["levels"], n_threads=threads)
+    dt = time.perf_counter() - t
+    return n_queries / dt, dt
+
+
+def run_reference(args, cfg, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, 16))
+    per_step = threads  # one full-shape query per thread per step
+    for _ in range(args.warmup if args.warmup < 1 else 1):  # one warm-up pass is enough on the CPU
+        cpu_sample(args, cfg, min(per_step, 2), min(threads, 2))
+    tot_q, tot_t = 0, 0.0
+    for _ in range(max(1, args.steps)):
+        qps, dt = cpu_sample(args, cfg, per_step, threads)
+        tot_q += per_step
+        tot_t += dt
+    v = tot_q / tot_t
+    sample = "%d full-shape queries per step, one per thread, %d step(s)" % (per_step, max(1, args.steps))
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "oracle/ C port of featurePnP/model.py (float64, CHW, reference operation order) on host threads; "
+                    "the Python reference cannot travel to the GPU box"}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    cfg = workload(args)
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, cfg, rank)
+        return
+
+    import torch.distributed as dist
+    import fmpnp_b200 as fm
+    from fmpnp_b200 import sharding, synth
+    from fmpnp_b200.binding import RESULT_DTYPE
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = fm.default_context()
+
+    B = args.queries
+    levels = cfg["levels"]
+    # ---- synthetic inputs, generated in HBM (seeded per global query index)
+    t_gen = time.perf_counter()
+    scenes = [synth.make_scene(rank * B + q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device=dev)
+              for q in range(B)]
+    active = torch.ones((B, args.points), dtype=torch.uint8, device=dev) if cfg["inlier_mask"] else None
+    probs = [fm.Problem.from_scene(sc, active=active[i] if active is not None else None) for i, sc in enumerate(scenes)]
+    probs_noact = [fm.Problem.from_scene(sc) for sc in scenes]
+    torch.cuda.synchronize()
+    gen_s = time.perf_counter() - t_gen
+    res_dev = torch.empty((B, RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
+
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+
+    def step(i=None):
+        """find_inliers -> active mask (written in place by the kernel), then the refinement kernel."""
+        if cfg["inlier_mask"]:
+            fm.find_inliers_batch(probs_noact, 0.8, loss=cfg["loss"], ctx=ctx, out=active)
+        if i is not None:
+            kev[i][0].record()
+        fm.refine_batch(probs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                        ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=res_dev)
+        if i is not None:
+            kev[i][1].record()
+        if world > 1:
+            return sharding.gather_result_records(res_dev, world * B)
+        return res_dev
+
+    for _ in range(max(args.warmup, 0)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    launches0 = ctx.launches
+    with ClockSampler(local_rank) as clk:
+        start.record()
+        for i in range(args.steps):
+            step(i)
+        end.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    total_ms = start.elapsed_time(end)
+    kern_ms = [a.elapsed_time(b) for a, b in kev]
+    launches = ctx.launches - launches0
+    if world > 1:
+        tmax = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        total_ms = float(tmax.item())
+    value = world * B * args.steps / (total_ms / 1e3)
+
+    # ---- roofline of the dominant kernel (refine_kernel), from the last step's results
+    res = res_dev.cpu().numpy().view(RESULT_DTYPE).reshape(B)
+    alg_bytes = float(res["gathered_rows"].astype(np.float64).sum()) * 4.0
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    k_ms = float(np.mean(kern_ms))
+    achieved = alg_bytes / (k_ms / 1e3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("refine_kernel_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    nominal = (args.iters + 1) * 4 * args.points * 4 * args.channels * B
+    roofline = {"bound": "hbm", "kernel": "fmpnp::refine_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernel_ms": k_ms,
+                "algorithmic_bytes_per_launch": alg_bytes,
+                "nominal_bytes_per_launch": float(nominal) if levels is None else None,
+                "share_of_step": k_ms * args.steps / total_ms}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": cfg, "roofline": roofline, "clocks": clk.summary(),
+            "gpu_launches": int(launches), "input_generation_s": gen_s,
+            "status_histogram": {str(k): int(v) for k, v in zip(*np.unique(res["status"], return_counts=True))},
+            "mean_evaluations_per_query": float(res["n_evaluations"].mean())}
+
+    # ---- e2e: same C ABI, inputs start in pinned HOST memory, results end in host memory
+    if not args.no_e2e:
+        E = min(args.e2e_queries, B)
+        names = ("F", "Gx", "Gy", "ref", "pts3D")
+        host = [{k: getattr(scenes[i], k).cpu().pin_memory() for k in names} for i in range(E)]
+        devbuf = [{k: torch.empty_like(getattr(scenes[i], k)) for k in names} for i in range(E)]
+        act_e = torch.ones((E, args.points), dtype=torch.uint8, device=dev) if cfg["inlier_mask"] else None
+        eprobs = [fm.Problem(devbuf[i]["F"], devbuf[i]["Gx"], devbuf[i]["Gy"], devbuf[i]["ref"], devbuf[i]["pts3D"],
+                             scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024,
+                             active=act_e[i] if act_e is not None else None) for i in range(E)]
+        eprobs_na = [fm.Problem(devbuf[i]["F"], None, None, devbuf[i]["ref"], devbuf[i]["pts3D"], scenes[i].K,
+                                scenes[i].R0, scenes[i].t0, 1024, 1024) for i in range(E)]
+        eres = torch.empty((E, RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
+        eres_host = torch.empty((E, RESULT_DTYPE.itemsize), dtype=torch.uint8).pin_memory()
+        h2d = sum(t.numel() * t.element_size() for d in host for t in d.values())
+        d2h = eres_host.numel()
+
+        def e2e_step():
+            for i in range(E):
+                for k in names:
+                    devbuf[i][k].copy_(host[i][k], non_blocking=True)
+            if cfg["inlier_mask"]:
+                fm.find_inliers_batch(eprobs_na, 0.8, loss=cfg["loss"], ctx=ctx, out=act_e)
+            fm.refine_batch(eprobs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                            ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=eres)
+            eres_host.copy_(eres, non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ksteps = max(2, min(args.steps, 5))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(ksteps):
+            e2e_step()
+        b.record()
+        torch.cuda.synchronize()
+        e_ms = a.elapsed_time(b)
+        if world > 1:
+            tm = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            e_ms = float(tm.item())
+        line["e2e"] = {"value": world * E * ksteps / (e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": int(d2h), "queries_per_step": E, "steps": ksteps,
+                       "h2d_gbs": h2d * ksteps / (e_ms / 1e3) / 1e9,
+                       "note": "HWC fp32 maps + descriptors + points in pinned host memory -> H2D -> find_inliers + "
+                               "refine kernels -> result records D2H, all inside the timed region (PCIe-bound)"}
+        del host, devbuf
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle port on a bounded sample
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        threads = max(1, min(cores, 16))
+        nq = args.cpu_queries or threads
+        try:
+            v, dt = cpu_sample(args, cfg, nq, threads, scenes=scenes)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "%d full-shape queries (seeds 0..%d of the same workload), one per thread, "
+                                              "%.1f s wall" % (nq, nq - 1, dt)}
+        except Exception as e:  # the baseline must never take the GPU number down with it
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "failed: %r" % (e,)}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -297,8 +297,8 @@ def compute_cost_batch(problems, ratio_threshold=None, ctx=None):
     return costs[:B], nsup[:B]
 
 
-def find_inliers_batch(problems, threshold, loss="squared_loss", barron_alpha=None, ctx=None):
-    """Batched find_inliers at (R0, t0); returns a uint8 device tensor [B][max N]."""
+def find_inliers_batch(problems, threshold, loss="squared_loss", barron_alpha=None, ctx=None, out=None):
+    """Batched find_inliers at (R0, t0); returns a uint8 device tensor [B][max N] (`out` if given)."""
     ctx = ctx or default_context()
     B = len(problems)
     dev = torch.device("cuda", ctx.device)
@@ -309,7 +309,13 @@ def find_inliers_batch(problems, threshold, loss="squared_loss", barron_alpha=No
         raise FmpnpError("find_inliers needs a threshold")
     n_stride = max([p.N for p in problems] + [1])
     arr = _problem_array(problems)
-    out = torch.zeros((max(B, 1), n_stride), dtype=torch.uint8, device=dev)
+    if out is None:
+        out = torch.zeros((max(B, 1), n_stride), dtype=torch.uint8, device=dev)
+    else:
+        if not (out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous() and out.dim() == 2
+                and out.shape[0] >= B and out.shape[1] >= n_stride):
+            raise FmpnpError("find_inliers out= must be a contiguous CUDA uint8 [>=B][>=max N] tensor")
+        n_stride = int(out.shape[1])
     rc = lib().fmpnp_find_inliers_batch(ctx._h, arr, B, lid, alpha, float(threshold), C.c_void_p(out.data_ptr()),
                                         n_stride, _stream_ptr())
     ctx.check(rc, "fmpnp_find_inliers_batch")

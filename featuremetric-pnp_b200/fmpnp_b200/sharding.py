@@ -1,0 +1,45 @@
+"""Query sharding across the GPUs of one box.
+
+Queries are independent: each rank owns a contiguous block of queries together with their
+feature maps, refines them with no per-iteration communication, and the fixed-size result
+records are gathered once at the end (NCCL all-gather over NVLink; gloo in the CPU tests).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_queries, rank, world_size):
+    """Contiguous block [lo, hi) of ceil(B / G) queries owned by `rank` (last ranks may be short)."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad rank / world size")
+    per = -(-n_queries // world_size)
+    lo = min(n_queries, rank * per)
+    hi = min(n_queries, lo + per)
+    return lo, hi
+
+
+def gather_result_records(local_records, n_queries, group=None):
+    """All-gathers per-rank result records.
+
+    local_records: uint8 tensor [n_local, record_bytes] (device tensor under NCCL, CPU under gloo)
+    holding this rank's block as laid out by shard_range.  Returns [n_queries, record_bytes] on
+    every rank, in global query order."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return local_records[:n_queries]
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    per = -(-n_queries // world)
+    rec = local_records.shape[1]
+    lo, hi = shard_range(n_queries, rank, world)
+    if local_records.shape[0] != hi - lo:
+        raise ValueError("rank %d holds %d records, expected %d" % (rank, local_records.shape[0], hi - lo))
+    pad = torch.zeros((per, rec), dtype=torch.uint8, device=local_records.device)
+    pad[: hi - lo] = local_records
+    out = torch.empty((world * per, rec), dtype=torch.uint8, device=local_records.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    return out[:n_queries]
+
+
+def records_to_numpy(records, dtype):
+    return np.ascontiguousarray(records.cpu().numpy()).view(dtype).reshape(-1)

@@ -146,7 +146,7 @@ def main():
     # 2. synthetic RobotCar-shaped scenes, small: 256 x 256 image over a 32 x 32 map keeps the
     #    reference's 8 px per cell; K scaled accordingly.
     Ks = ((100.0, 0.0, 127.055733), (0.0, 100.0, 124.546844), (0.0, 0.0, 1.0))
-    base = dict(Hf=32, Wf=32, im_width=256, im_height=256, K=Ks)
+    base = dict(Hf=32, Wf=32, im_width=256, im_height=256, K=Ks, noise_sigma=0.01)
     mk = lambda q, **kw: synth.make_scene(q, device="cpu", **{**base, **kw})  # noqa: E731
     GS = 1.0 / 64  # un-normalised Sobel (x8) on 8 px cells -> d/dpixel: real Gauss-Newton sized steps
     # raw reference behaviour (Jacobian 64x too large -> tiny steps, cost hardly moves)
