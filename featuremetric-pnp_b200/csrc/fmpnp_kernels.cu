@@ -475,7 +475,8 @@ __device__ __forceinline__ void hist_slices(const LaunchParams& p, int qi, int e
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams p) {
+template <int MODE>
+__device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     extern __shared__ __align__(128) unsigned char ring[];
     __shared__ Shared sh;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -520,7 +521,7 @@ __global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams 
         }
         __syncthreads();
 
-        if (p.mode == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
+        if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
             c.c0 = 0;
             c.Cl = q.C;
             c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
@@ -536,7 +537,7 @@ __global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams 
             }
             continue;
         }
-        if (p.mode == kModeFindInliers) {  // find_inliers (model.py:131-152)
+        if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152)
             c.c0 = 0;
             c.Cl = q.C;
             c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
@@ -549,6 +550,7 @@ __global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams 
             continue;
         }
 
+        if (MODE != kModeRefine) continue;
         // ------------------------------------------------------------------ refine
         if (tid == 0) {
             sh.status = FMPNP_STATUS_OK;
@@ -698,6 +700,15 @@ __global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams 
     }
 }
 
+// Three entry points over the same persistent body, so profilers see them by name.
+__global__ void __launch_bounds__(kThreads, 2) refine_kernel(const LaunchParams p) { persistent_body<kModeRefine>(p); }
+__global__ void __launch_bounds__(kThreads, 2) compute_cost_kernel(const LaunchParams p) {
+    persistent_body<kModeComputeCost>(p);
+}
+__global__ void __launch_bounds__(kThreads, 2) find_inliers_kernel(const LaunchParams p) {
+    persistent_body<kModeFindInliers>(p);
+}
+
 // ---------------------------------------------------------------------------------------------
 // CHW (float32 / float64) -> HWC float32 pack: a (C) x (Hf*Wf) transpose through shared memory.
 // ---------------------------------------------------------------------------------------------
@@ -730,11 +741,20 @@ cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, 
 size_t refine_static_smem_bytes() { return sizeof(Shared); }
 
 cudaError_t refine_set_max_dynamic_smem(int bytes) {
-    return cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    cudaError_t e = cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(compute_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(find_inliers_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    return e;
 }
 
 cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream) {
-    refine_kernel<<<grid, kThreads, ring_bytes, stream>>>(p);
+    switch (p.mode) {
+        case kModeComputeCost: compute_cost_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
+        case kModeFindInliers: find_inliers_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
+        default: refine_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
+    }
     return cudaGetLastError();
 }
 

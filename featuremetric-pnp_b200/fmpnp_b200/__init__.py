@@ -33,6 +33,8 @@ from .binding import (  # noqa: F401
     refine_batch,
 )
 
+from . import ops  # noqa: E402,F401  (registers torch.ops.fmpnp.*)
+
 __all__ = [
     "LOSS_IDS", "STATUS_OK", "STATUS_EMPTY_SUPPORT", "STATUS_NAN_STEP", "STATUS_NO_INITIAL_COST", "Context",
     "FmpnpError", "Problem", "compute_cost_batch", "default_context", "find_inliers_batch", "lib", "lib_path",

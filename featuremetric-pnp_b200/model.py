@@ -60,7 +60,7 @@ def _pack_map(m):
     if src.dtype not in (torch.float32, torch.float64):
         src = src.double()
     src = src.to(_device(), non_blocking=True).contiguous()
-    out = _fm.pack_chw_to_hwc(src)
+    out = torch.ops.fmpnp.pack_chw_to_hwc(src)
     _PACK_CACHE[key] = (m, out)  # keeping `m` alive keeps data_ptr unique
     while len(_PACK_CACHE) > _PACK_CACHE_MAX:
         _PACK_CACHE.popitem(last=False)
@@ -130,12 +130,20 @@ class sparseFeaturePnP(nn.Module):
 
     # -- shared tail of forward / multilevel_optimization ---------------------------------------
     def _run(self, prob, levels, track):
-        out = _fm.refine_batch([prob], self.iterations, loss=self.loss_fn, lambda_=self.lambda_,
-                               ratio_threshold=self.ratio_threshold_, levels=levels, track=bool(track),
-                               solver=self.solver)
-        r = out["results"][0]
+        """One query through torch.ops.fmpnp.refine_batch (PyTorch custom op -> C ABI -> CUDA kernel)."""
+        loss_id, alpha = _fm.loss_id_of(self.loss_fn)
+        rt = float("nan") if self.ratio_threshold_ is None else float(self.ratio_threshold_)
+        solver = {"cholesky": 0, "lu": 1}[self.solver]
+        opts = torch.tensor([float(self.iterations), float(loss_id), alpha, float(self.lambda_), rt, float(solver)],
+                            dtype=torch.float64)
+        lv = torch.tensor(levels if levels else [], dtype=torch.int32).reshape(-1, 2)
+        outs = torch.ops.fmpnp.refine_batch(
+            [prob.F], [prob.Gx], [prob.Gy], [prob.ref], [prob.pts3D], torch.from_numpy(prob.K.reshape(1, 3, 3)),
+            torch.from_numpy(prob.R0.reshape(1, 3, 3)), torch.from_numpy(prob.t0.reshape(1, 3)),
+            torch.tensor([[prob.im_width, prob.im_height]], dtype=torch.int32), opts, lv, bool(track))
+        r = outs[0].cpu().numpy().view(_fm.binding.RESULT_DTYPE).reshape(-1)[0]
         if track:
-            h = out["history"]
+            h = {k: v.cpu().numpy() for k, v in zip(_fm.ops.HISTORY_KEYS, outs[1:])}
             n = int(h["len"][0])
             N = prob.N
             for e in range(n):
