@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
+    ap.add_argument("--sort-points", action="store_true",
+                    help="experiment: order each query's points by feature-map cell (DRAM page / TLB locality)")
+    ap.add_argument("--outliers", type=float, default=None, help="outlier fraction (default: 0 for cfg2, 0.1 otherwise)")
     return ap.parse_args()
 
 
@@ -229,8 +232,17 @@ def main():
     levels = cfg["levels"]
     # ---- synthetic inputs, generated in HBM (seeded per global query index)
     t_gen = time.perf_counter()
-    scenes = [synth.make_scene(rank * B + q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device=dev)
-              for q in range(B)]
+    outl = args.outliers if args.outliers is not None else (0.0 if args.config == "gn_inlier" else 0.1)
+    scenes = [synth.make_scene(rank * B + q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device=dev,
+                               outlier_frac=outl) for q in range(B)]
+    if args.sort_points:
+        for sc in scenes:
+            P = sc.pts3D.cpu()
+            u = torch.round(sc.K[0, 0] * P[:, 0] / P[:, 2] + sc.K[0, 2]).long().clamp(0, 1023)
+            v = torch.round(sc.K[1, 1] * P[:, 1] / P[:, 2] + sc.K[1, 2]).long().clamp(0, 1023)
+            order = torch.argsort((v * args.map // 1024) * args.map + (u * args.map // 1024)).to(dev)
+            sc.pts3D = sc.pts3D[order].contiguous()
+            sc.ref = sc.ref[order].contiguous()
     active = torch.ones((B, args.points), dtype=torch.uint8, device=dev) if cfg["inlier_mask"] else None
     probs = [fm.Problem.from_scene(sc, active=active[i] if active is not None else None) for i, sc in enumerate(scenes)]
     probs_noact = [fm.Problem.from_scene(sc) for sc in scenes]
@@ -306,7 +318,7 @@ def main():
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": cfg, "roofline": roofline, "clocks": clk.summary(),
+            "dtype": "f64", "data": "synthetic", "config": dict(cfg, sort_points=bool(args.sort_points), outlier_frac=outl), "roofline": roofline, "clocks": clk.summary(),
             "gpu_launches": int(launches), "input_generation_s": gen_s,
             "status_histogram": {str(k): int(v) for k, v in zip(*np.unique(res["status"], return_counts=True))},
             "mean_evaluations_per_query": float(res["n_evaluations"].mean())}

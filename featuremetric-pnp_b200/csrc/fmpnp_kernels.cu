@@ -171,49 +171,73 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
         const int CH = (c.Cl <= chMax) ? c.Cl : (chMax >= 128 ? (chMax & ~127) : chMax);
         const int nCh = (c.Cl + CH - 1) / CH;
         if (warp == 0) {
-            // ---------------- producer: float64 projection + TMA issue
+            // ---------------- producer: float64 projection + TMA issue.
+            // Four lanes serve each consumer warp ("feeder" fw): lane fr issues the bulk copy of row
+            // fr.  The feeders poll their slot's `empty` barrier with the non-blocking test_wait in a
+            // warp-convergent loop -- no lane ever blocks, so one slow consumer never stalls the
+            // other seven sub-rings and the warp does not serialise on divergent spin loops.
+            constexpr int LPF = 32 / kConsumerWarps;  // lanes per feeder == points per feeder per batch
+            static_assert(LPF >= 4, "need one lane per staged row");
+            const int fw = lane / LPF, fr = lane % LPF;
             for (int base = 0; base < N; base += 32) {
                 const int n = base + lane;
                 int cell = -1;
                 if (n < N) cell = project_and_flag(c, R, t, n);
                 sh.cellbuf[lane] = cell;
                 __syncwarp();
-                if (lane < kConsumerWarps) {
-                    for (int j = lane; j < 32; j += kConsumerWarps) {
-                        const int cj = sh.cellbuf[j];
-                        if (cj < 0) continue;
-                        const int nj = base + j;
-                        const float* srcF = q.F + (size_t)cj * q.C + c.c0;
-                        const float* srcGx = GRAD ? q.Gx + (size_t)cj * q.C + c.c0 : nullptr;
-                        const float* srcGy = GRAD ? q.Gy + (size_t)cj * q.C + c.c0 : nullptr;
-                        const float* srcR = q.ref + (size_t)nj * q.C + c.c0;
-                        for (int ch = 0; ch < nCh; ++ch) {
-                            const int off = ch * CH;
-                            const int cnt = min(CH, c.Cl - off);
-                            const uint32_t rowB = (uint32_t)cnt * 4u;
-                            const int slot = lane * c.depth + rp.pos;
-                            mbar_wait(&sh.empty[slot], rp.phase ^ 1u);
-                            sh.meta[slot] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
-                            mbar_arrive_expect_tx(&sh.full[slot], (uint32_t)ROWS * rowB);
-                            unsigned char* dst = c.ring + (size_t)slot * c.slot_bytes;
-                            tma_bulk_g2s(dst, srcF + off, rowB, &sh.full[slot]);
-                            if (GRAD) {
-                                tma_bulk_g2s(dst + rowB, srcGx + off, rowB, &sh.full[slot]);
-                                tma_bulk_g2s(dst + 2 * rowB, srcGy + off, rowB, &sh.full[slot]);
-                            }
-                            tma_bulk_g2s(dst + (ROWS - 1) * rowB, srcR + off, rowB, &sh.full[slot]);
-                            rp.advance(c.depth);
+                int jj = 0, ch = 0;
+                for (;;) {
+                    while (jj < LPF && sh.cellbuf[fw + kConsumerWarps * jj] < 0) ++jj;  // next supported point
+                    const bool have = jj < LPF;
+                    if (!__any_sync(0xffffffffu, have)) break;
+                    const int slot = fw * c.depth + rp.pos;
+                    const bool go = have && mbar_test(&sh.empty[slot], rp.phase ^ 1u);
+                    const int j = fw + kConsumerWarps * (have ? jj : 0);
+                    const int cj = sh.cellbuf[j], nj = base + j;
+                    const int off = ch * CH;
+                    const uint32_t rowB = (uint32_t)min(CH, c.Cl - off) * 4u;
+                    if (go && fr == 0) {
+                        sh.meta[slot] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
+                        mbar_arrive_expect_tx(&sh.full[slot], (uint32_t)ROWS * rowB);
+                    }
+                    __syncwarp();
+                    if (go && fr < ROWS) {
+                        const float* src;
+                        if (fr == ROWS - 1)
+                            src = q.ref + (size_t)nj * q.C;
+                        else
+                            src = (fr == 0 ? q.F : (fr == 1 ? q.Gx : q.Gy)) + (size_t)cj * q.C;
+                        tma_bulk_g2s(c.ring + (size_t)slot * c.slot_bytes + fr * rowB, src + c.c0 + off, rowB,
+                                     &sh.full[slot]);
+                    }
+                    if (go) {
+                        rp.advance(c.depth);
+                        if (++ch == nCh) {
+                            ch = 0;
+                            ++jj;
                         }
                     }
+                    if (!__any_sync(0xffffffffu, go)) __nanosleep(40);
                 }
                 __syncwarp();
             }
-            if (lane < kConsumerWarps) {  // end-of-evaluation sentinel for "my" consumer warp
-                const int slot = lane * c.depth + rp.pos;
-                mbar_wait(&sh.empty[slot], rp.phase ^ 1u);
-                sh.meta[slot] = make_int2(-1, 0);
-                mbar_arrive(&sh.full[slot]);
-                rp.advance(c.depth);
+            {  // end-of-evaluation sentinel for every consumer warp
+                bool posted = false;
+                for (;;) {
+                    if (!posted) {
+                        const int slot = fw * c.depth + rp.pos;
+                        if (mbar_test(&sh.empty[slot], rp.phase ^ 1u)) {
+                            if (fr == 0) {
+                                sh.meta[slot] = make_int2(-1, 0);
+                                mbar_arrive(&sh.full[slot]);
+                            }
+                            rp.advance(c.depth);
+                            posted = true;
+                        }
+                    }
+                    if (__all_sync(0xffffffffu, posted)) break;
+                    __nanosleep(40);
+                }
             }
         } else {
             // ---------------- consumers: warp w drains sub-ring w

@@ -1,0 +1,330 @@
+"""GPU: shapes and exit paths beyond the golden fixtures, checked against the oracle, plus
+size-independent properties at the BASELINE.json sizes (N = 4096, C = 1024, 128 x 128 maps)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from util import COST_RTOL, ROT_TOL_DEG, TRANS_TOL_M, assert_costs_close, rot_angle_deg
+
+pytestmark = pytest.mark.gpu
+TIGHT = 1e-9
+KS = ((100.0, 0.0, 127.055733), (0.0, 100.0, 124.546844), (0.0, 0.0, 1.0))
+SMALL = dict(Hf=32, Wf=32, im_width=256, im_height=256, K=KS)
+
+
+def fm():
+    import fmpnp_b200
+    return fmpnp_b200
+
+
+def same_records(a, b):
+    """Field-wise bit equality of fmpnp_result records (the struct has 4 padding bytes)."""
+    a, b = np.atleast_1d(a), np.atleast_1d(b)
+    return a.shape == b.shape and all(
+        np.ascontiguousarray(a[f]).tobytes() == np.ascontiguousarray(b[f]).tobytes() for f in a.dtype.names)
+
+
+def synth():
+    from fmpnp_b200 import synth as s
+    return s
+
+
+def to_problem(sc, active=None, R0=None, t0=None):
+    dev = "cuda"
+    return fm().Problem(sc.F.to(dev), sc.Gx.to(dev), sc.Gy.to(dev), sc.ref.to(dev), sc.pts3D.to(dev), sc.K,
+                        sc.R0 if R0 is None else R0, sc.t0 if t0 is None else t0, sc.im_width, sc.im_height,
+                        active=None if active is None else torch.as_tensor(active, dtype=torch.uint8, device=dev))
+
+
+def run_oracle(sc, n_iters, loss, lambda_, ratio, levels=None, sel=None, R0=None, t0=None):
+    inp = sc.reference_inputs()
+    pts, ref = inp["pts3D"].numpy(), inp["feature_ref"].numpy()
+    if sel is not None:
+        pts, ref = np.ascontiguousarray(pts[sel]), np.ascontiguousarray(ref[sel])
+    args = (pts, ref, inp["feature_map_query"].numpy(), inp["feature_grad_x"].numpy(), inp["feature_grad_y"].numpy(),
+            inp["K"].numpy(), sc.im_width, sc.im_height, inp["R_init"].numpy() if R0 is None else np.asarray(R0),
+            inp["t_init"].numpy() if t0 is None else np.asarray(t0), n_iters)
+    kw = dict(loss=loss, lambda_=lambda_, ratio_threshold=ratio, track=True)
+    return oracle.forward(*args, **kw) if levels is None else oracle.multilevel(levels, *args, **kw)
+
+
+def compare(name, res, hist, o, b=0, use_ratio=False, sel=None):
+    tr = o["track"]
+    n = int(hist["len"][b])
+    assert n == len(tr["costs"]), "%s: %d entries vs oracle %d" % (name, n, len(tr["costs"]))
+    N = tr["points2d"].shape[1] if n else 0
+    px, mk, kp = hist["points2d"][b, :n], hist["mask"][b, :n].astype(bool), hist["kept"][b, :n].astype(bool)
+    if sel is not None:
+        px, mk, kp = px[:, sel], mk[:, sel], kp[:, sel]
+    else:
+        px, mk, kp = px[:, :N], mk[:, :N], kp[:, :N]
+    if n:
+        assert np.array_equal(px, tr["points2d"]), name + ": pixel indices"
+        assert np.array_equal(mk, tr["mask"]), name + ": support mask"
+        if use_ratio:
+            assert np.array_equal(kp, tr["threshold_mask"]), name + ": ratio mask"
+        assert_costs_close(hist["costs"][b, :n], tr["costs"], COST_RTOL, name)
+        assert_costs_close(hist["costs"][b, :n], tr["costs"], TIGHT, name + " (tight)")
+    R, t = np.array(res["R"]).reshape(3, 3), np.array(res["t"])
+    assert rot_angle_deg(R, o["R"]) <= ROT_TOL_DEG and np.abs(t - o["t"]).max() <= TRANS_TOL_M, name + ": pose"
+    assert np.abs(R - o["R"]).max() < 1e-8 and np.abs(t - o["t"]).max() < 1e-8, name + ": pose (tight)"
+    assert int(res["status"]) == int(o["status"]), "%s: status %d vs oracle %d" % (name, res["status"], o["status"])
+
+
+# ----------------------------------------------------------------------------------------------
+# wide channel counts: rows longer than a staging slot are split into channel chunks
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("C,levels", [(1024, None), (640, None), (1024, [(512, 1024), (128, 512), (0, 128)]),
+                                      (2048, [(1024, 2048), (256, 1024), (0, 256)]), (516, None), (20, [(8, 20), (0, 8)])])
+def test_wide_and_chunked_channels(C, levels):
+    sc = synth().make_scene(21, N=200, C=C, Hf=16, Wf=16, im_width=128, im_height=128,
+                            K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
+                            outlier_frac=0.1)
+    out = fm().refine_batch([to_problem(sc)], 6, loss="geman_mcclure_loss", lambda_=0.01, levels=levels, track=True)
+    o = run_oracle(sc, 6, "geman_mcclure_loss", 0.01, None, levels)
+    compare("C=%d" % C, out["results"][0], out["history"], o)
+
+
+# ----------------------------------------------------------------------------------------------
+# a ragged batch: different N per query, one launch
+# ----------------------------------------------------------------------------------------------
+def test_ragged_batch_matches_oracle_and_single_runs():
+    Ns = [1, 7, 33, 150, 257, 64, 300, 96, 5, 211]
+    scs = [synth().make_scene(40 + i, N=n, C=32, grad_scale=1.0 / 64, outlier_frac=0.1, **SMALL) for i, n in enumerate(Ns)]
+    probs = [to_problem(sc) for sc in scs]
+    out = fm().refine_batch(probs, 8, loss="cauchy_loss", lambda_=0.01, ratio_threshold=0.9, track=True)
+    for i, sc in enumerate(scs):
+        o = run_oracle(sc, 8, "cauchy_loss", 0.01, 0.9)
+        compare("ragged[%d] N=%d" % (i, Ns[i]), out["results"][i], out["history"], o, b=i, use_ratio=True)
+    # the same queries one by one are bit-identical to the batch (deterministic per query)
+    for i in (0, 3, 9):
+        single = fm().refine_batch([probs[i]], 8, loss="cauchy_loss", lambda_=0.01, ratio_threshold=0.9)["results"][0]
+        assert same_records(single, out["results"][i])
+
+
+def test_more_queries_than_resident_ctas():
+    """B > 2 * #SM: the persistent grid loops over the work counter."""
+    sc = synth().make_scene(77, N=40, C=8, grad_scale=1.0 / 64, **SMALL)
+    p = to_problem(sc)
+    B = 700
+    out = fm().refine_batch([p] * B, 5, loss="squared_loss", lambda_=0.01)
+    r = out["results"]
+    assert len(r) == B
+    assert same_records(r, np.repeat(r[:1], B))
+    o = run_oracle(sc, 5, "squared_loss", 0.01, None)
+    assert np.abs(np.array(r[0]["R"]).reshape(3, 3) - o["R"]).max() < 1e-8
+
+
+# ----------------------------------------------------------------------------------------------
+# exit paths
+# ----------------------------------------------------------------------------------------------
+def test_no_supported_point_returns_initial_pose():
+    sc = synth().make_scene(50, N=30, C=8, **SMALL)
+    t_far = sc.t0.clone()
+    t_far[0] += 1000.0  # everything projects outside the image
+    out = fm().refine_batch([to_problem(sc, t0=t_far)], 5, track=True)
+    r = out["results"][0]
+    assert int(r["status"]) == fm().STATUS_EMPTY_SUPPORT and int(out["history"]["len"][0]) == 0
+    assert np.array_equal(np.array(r["R"]).reshape(3, 3), sc.R0.numpy()) and np.array_equal(np.array(r["t"]), t_far.numpy())
+    assert int(r["best_num_inliers"]) == -1 and np.isnan(r["best_cost"])
+    o = run_oracle(sc, 5, "squared_loss", 0.01, None, t0=t_far.numpy())
+    assert o["status"] == oracle.EMPTY_SUPPORT and o["has_best"] == 0
+    # multilevel: compute_cost is None -> initial pose, NO_INITIAL_COST
+    out = fm().refine_batch([to_problem(sc, t0=t_far)], 5, levels=[(4, 8), (0, 4)])
+    assert int(out["results"][0]["status"]) == fm().STATUS_NO_INITIAL_COST
+    assert np.array_equal(np.array(out["results"][0]["t"]), t_far.numpy())
+    c, ns = fm().compute_cost_batch([to_problem(sc, t0=t_far)])
+    assert int(ns[0]) == 0 and torch.isnan(c[0])
+
+
+def test_zero_points():
+    sc = synth().make_scene(51, N=4, C=8, **SMALL)
+    sc.pts3D = sc.pts3D[:0].contiguous()
+    sc.ref = sc.ref[:0].contiguous()
+    out = fm().refine_batch([to_problem(sc)], 3, track=True)
+    assert int(out["results"][0]["status"]) == fm().STATUS_EMPTY_SUPPORT
+    assert fm().find_inliers_batch([to_problem(sc)], 0.8).shape[0] == 1
+
+
+def test_nan_step_breaks_and_returns_best():
+    """Gauss-Newton (lambda_ = 0) with identically zero gradient maps: H = 0, g = 0, LU meets a
+    zero pivot, the step is 0/0 = NaN, the loop is left and the best (= initial) pose returned
+    (the intent of model.py:411-413)."""
+    sc = synth().make_scene(52, N=20, C=4, grad_scale=0.0, **SMALL)
+    assert float(sc.Gx.abs().max()) == 0.0
+    o = run_oracle(sc, 5, "squared_loss", 0.0, None)
+    assert o["status"] == oracle.NAN_STEP and len(o["track"]["costs"]) == 1
+    for solver in ("lu", "cholesky"):
+        out = fm().refine_batch([to_problem(sc)], 5, loss="squared_loss", lambda_=0.0, track=True, solver=solver)
+        compare("nan-step/" + solver, out["results"][0], out["history"], o)
+        assert int(out["results"][0]["status"]) == fm().STATUS_NAN_STEP
+        assert np.array_equal(np.array(out["results"][0]["R"]).reshape(3, 3), sc.R0.numpy())
+    # with damping the same problem is solvable (step = 0): runs to the end, pose unchanged
+    out = fm().refine_batch([to_problem(sc)], 5, loss="squared_loss", lambda_=0.01, track=True)
+    o2 = run_oracle(sc, 5, "squared_loss", 0.01, None)
+    compare("zero-gradient damped", out["results"][0], out["history"], o2)
+
+
+def test_ratio_test_that_removes_every_point():
+    """One supported point: |rho| < thr * max|rho| is false for it -> zero survivors, cost = nan,
+    H = g = 0; the reference then keeps 'accepting' nan costs. Must match the oracle exactly."""
+    sc = synth().make_scene(53, N=1, C=8, **SMALL)
+    o = run_oracle(sc, 4, "squared_loss", 0.01, 0.8)
+    out = fm().refine_batch([to_problem(sc)], 4, loss="squared_loss", lambda_=0.01, ratio_threshold=0.8, track=True)
+    compare("ratio-all-removed", out["results"][0], out["history"], o, use_ratio=True)
+    assert np.isnan(out["history"]["costs"][0, 0]) and int(out["results"][0]["best_num_inliers"]) == 0
+
+
+def test_step_that_leaves_the_image_returns_current_pose():
+    """Tiny gradients -> tiny H -> huge undamped step -> no supported point at the trial pose:
+    forward returns the CURRENT pose (model.py:441-445)."""
+    sc = synth().make_scene(54, N=60, C=8, grad_scale=1e-9, **SMALL)
+    o = run_oracle(sc, 6, "squared_loss", 0.0, None)
+    out = fm().refine_batch([to_problem(sc)], 6, loss="squared_loss", lambda_=0.0, track=True, solver="lu")
+    compare("fly-away", out["results"][0], out["history"], o)
+
+
+def test_points_behind_the_camera_are_not_filtered():
+    sc = synth().make_scene(55, N=80, C=8, grad_scale=1.0 / 64, **SMALL)
+    pts = sc.pts3D.clone()
+    pts[::3] *= -1.0  # mirrored through the camera centre: same pixel, negative depth
+    sc.pts3D = pts
+    o = run_oracle(sc, 5, "squared_loss", 0.01, None)
+    out = fm().refine_batch([to_problem(sc)], 5, loss="squared_loss", lambda_=0.01, track=True)
+    compare("behind-camera", out["results"][0], out["history"], o)
+    assert o["track"]["mask"][0][::3].any()
+
+
+def test_active_mask_equals_compaction():
+    """fmpnp_problem.active == passing pts3D[inliers], feature_ref[inliers] (optimize_feature_pnp.py:43-44)."""
+    sc = synth().make_scene(56, N=150, C=16, grad_scale=1.0 / 64, outlier_frac=0.2, **SMALL)
+    inl = fm().find_inliers_batch([to_problem(sc)], 0.8, loss="squared_loss")[0].cpu().numpy().astype(bool)
+    inp = sc.reference_inputs()
+    inl_o = oracle.find_inliers(inp["pts3D"].numpy(), sc.R0.numpy(), sc.t0.numpy(), inp["feature_map_query"].numpy(),
+                                inp["feature_ref"].numpy(), sc.K.numpy(), sc.im_width, sc.im_height, 0.8)
+    assert np.array_equal(inl, inl_o) and 0 < inl.sum() < 150
+    sel = np.nonzero(inl)[0]
+    o = run_oracle(sc, 8, "squared_loss", 0.0, 0.8, sel=sel)
+    out = fm().refine_batch([to_problem(sc, active=inl.astype(np.uint8))], 8, loss="squared_loss", lambda_=0.0,
+                            ratio_threshold=0.8, track=True)
+    compare("active-mask", out["results"][0], out["history"], o, use_ratio=True, sel=sel)
+
+
+def test_unaligned_views_take_the_generic_path():
+    """Descriptor / map tensors whose base address is not 16-byte aligned (a slice of a larger buffer)."""
+    sc = synth().make_scene(57, N=64, C=16, grad_scale=1.0 / 64, **SMALL)
+    dev = "cuda"
+
+    def misalign(t):
+        buf = torch.empty(t.numel() + 1, dtype=t.dtype, device=dev)
+        v = buf[1:].view(t.shape)
+        v.copy_(t)
+        assert v.data_ptr() % 16 != 0
+        return v
+
+    p = fm().Problem(misalign(sc.F), misalign(sc.Gx), misalign(sc.Gy), misalign(sc.ref), sc.pts3D.to(dev), sc.K, sc.R0,
+                     sc.t0, sc.im_width, sc.im_height)
+    out = fm().refine_batch([p], 6, loss="geman_mcclure_loss", lambda_=0.01, track=True)
+    o = run_oracle(sc, 6, "geman_mcclure_loss", 0.01, None)
+    compare("unaligned", out["results"][0], out["history"], o)
+
+
+def test_argument_errors_are_reported_not_crashed():
+    sc = synth().make_scene(58, N=16, C=8, **SMALL)
+    p = to_problem(sc)
+    with pytest.raises(fm().FmpnpError):
+        fm().refine_batch([p], 5, levels=[(0, 9)])  # slice outside the 8 channels
+    with pytest.raises(fm().FmpnpError):
+        fm().refine_batch([p], -1)
+    with pytest.raises(fm().FmpnpError):
+        fm().Problem(sc.F, sc.Gx, sc.Gy, sc.ref, sc.pts3D, sc.K, sc.R0, sc.t0, 256, 256)  # CPU tensors
+
+
+# ----------------------------------------------------------------------------------------------
+# BASELINE sizes: N = 4096, C = 1024, 128 x 128 maps, 1024 x 1024 image
+# ----------------------------------------------------------------------------------------------
+def torch_eval(sc, R, t, dev="cuda"):
+    """Plain torch float64 restatement of ONE linearisation (squared loss, no ratio test) on the
+    GPU: returns cost mean, H (6x6), g (6), pixel indices and support mask."""
+    pts = sc.pts3D.to(dev)
+    R, t, K = (torch.as_tensor(x, dtype=torch.float64, device=dev) for x in (R, t, sc.K))
+    P = (R @ pts.T).T + t
+    q = (K @ P.T).T
+    px = torch.round(q[:, :2] / q[:, 2:3]).to(torch.int32) - 1
+    m = (px[:, 0] >= 0) & (px[:, 1] >= 0) & (px[:, 0] < sc.im_width) & (px[:, 1] < sc.im_height)
+    Hf, Wf, C = sc.F.shape
+    row = torch.div(px[m, 1].long() * Hf, sc.im_height, rounding_mode="floor")
+    col = torch.div(px[m, 0].long() * Wf, sc.im_width, rounding_mode="floor")
+    cell = row * Wf + col
+    F, Gx, Gy = (x.to(dev).reshape(Hf * Wf, C) for x in (sc.F, sc.Gx, sc.Gy))
+    e = F[cell].double() - sc.ref.to(dev)[m].double()
+    gx, gy = Gx[cell].double(), Gy[cell].double()
+    Ps = P[m]
+    X, Y, Z = Ps[:, 0], Ps[:, 1], Ps[:, 2]
+    fx, fy = K[0, 0], K[1, 1]
+    zero = torch.zeros_like(X)
+    J1 = torch.stack([fx / Z, zero, -fx * X / Z / Z, zero, fy / Z, -fy * Y / Z / Z], -1).reshape(-1, 2, 3)
+    sk = torch.stack([zero, -Z, Y, Z, zero, -X, -Y, X, zero], -1).reshape(-1, 3, 3)
+    JpT = torch.cat([torch.eye(3, dtype=torch.float64, device=dev).expand(len(X), 3, 3), -sk], -1)
+    A = J1 @ JpT  # n,2,6
+    S = torch.stack([(gx * gx).sum(-1), (gx * gy).sum(-1), (gx * gy).sum(-1), (gy * gy).sum(-1)], -1).reshape(-1, 2, 2)
+    b = torch.stack([(gx * e).sum(-1), (gy * e).sum(-1)], -1)
+    H = (A.transpose(1, 2) @ S @ A).sum(0)
+    g = (A.transpose(1, 2) @ b[..., None]).sum(0)[:, 0]
+    cost = (0.5 * (e * e).sum(-1)).mean()
+    return cost.item(), H.cpu().numpy(), g.cpu().numpy(), px.cpu().numpy(), m.cpu().numpy()
+
+
+@pytest.fixture(scope="module")
+def big_scenes():
+    s = synth()
+    return [s.make_scene(900 + q, N=4096, C=1024, Hf=128, Wf=128, device="cuda", grad_scale=1.0 / 64) for q in range(3)]
+
+
+def test_full_size_first_step_against_torch_fp64(big_scenes):
+    """At full size the oracle would take minutes; one LM step is checked against a vectorised
+    torch float64 evaluation instead (cost, pixel indices, mask, and the pose after one step)."""
+    for sc in big_scenes:
+        p = fm().Problem.from_scene(sc)
+        out = fm().refine_batch([p], 1, loss="squared_loss", lambda_=0.01, track=True)
+        h, r = out["history"], out["results"][0]
+        cost, H, g, px, m = torch_eval(sc, sc.R0, sc.t0)
+        assert np.array_equal(h["points2d"][0, 0], px) and np.array_equal(h["mask"][0, 0].astype(bool), m)
+        assert abs(h["costs"][0, 0] - cost) <= 1e-11 * abs(cost)
+        Hd = H + 0.01 * np.diag(np.diag(H) + 1e-9)
+        delta = -np.linalg.solve(Hd, g)
+        dr = oracle.so3exp(delta[3:])
+        Rn, tn = dr @ sc.R0.numpy(), dr @ sc.t0.numpy() + delta[:3]
+        np.testing.assert_allclose(h["Rs"][0, 1], Rn, rtol=0, atol=1e-10)
+        np.testing.assert_allclose(h["ts"][0, 1], tn, rtol=0, atol=1e-9)
+        cost1, _, _, px1, m1 = torch_eval(sc, Rn, tn)
+        assert np.array_equal(h["points2d"][0, 1], px1) and np.array_equal(h["mask"][0, 1].astype(bool), m1)
+        assert abs(h["costs"][0, 1] - cost1) <= 1e-11 * abs(cost1)
+        assert int(r["gathered_rows"]) == (int(m.sum()) + int(m1.sum())) * 1024 * 4
+
+
+def test_full_size_fixed_point_and_determinism(big_scenes):
+    s = synth()
+    sc = s.make_scene(950, N=4096, C=1024, Hf=128, Wf=128, device="cuda", noise_sigma=0.0, grad_scale=1.0 / 64)
+    eye, zero = torch.eye(3, dtype=torch.float64), torch.zeros(3, dtype=torch.float64)
+    p = fm().Problem.from_scene(sc, R0=eye, t0=zero)
+    out = fm().refine_batch([p], 20, loss="geman_mcclure_loss", lambda_=0.01, track=True)
+    r, h = out["results"][0], out["history"]
+    # descriptors equal the map at the ground-truth cells and the pose is the ground truth:
+    # zero residual -> zero gradient -> zero step: cost stays 0 and the pose does not move at all
+    assert int(h["len"][0]) == 21 and np.all(h["costs"][0, :21] == 0.0)
+    assert np.array_equal(np.array(r["R"]).reshape(3, 3), np.eye(3)) and np.array_equal(np.array(r["t"]), np.zeros(3))
+    # determinism + batch independence at full size, LM with rejections possible
+    probs = [fm().Problem.from_scene(x) for x in big_scenes]
+    a = fm().refine_batch(probs, 20, loss="geman_mcclure_loss", lambda_=0.01)["results"]
+    b = fm().refine_batch(probs[::-1], 20, loss="geman_mcclure_loss", lambda_=0.01)["results"][::-1]
+    assert same_records(a, b)
+    assert np.all(a["status"] == 0) and np.all(a["n_evaluations"] == 21)
+    assert np.all(a["best_cost"] <= a["initial_cost"])
+    # pyramid at full size: every level's evaluations are counted, compute_cost included
+    lv = [(512, 1024), (128, 512), (0, 128)]
+    c = fm().refine_batch(probs, 20, loss="squared_loss", lambda_=0.01, levels=lv)["results"]
+    assert np.all(c["n_evaluations"] == 1 + 3 * 21)
+    costs, nsup = fm().compute_cost_batch(probs)
+    assert np.allclose(c["initial_cost"], costs.cpu().numpy(), rtol=0, atol=0)
