@@ -11,6 +11,10 @@
 
 using namespace fmpnp;
 
+struct Geometry_last {
+    int grid, cluster, ring_bytes, ctas;
+};
+
 struct fmpnp_ctx {
     int device = 0;
     int sm_count = 0;
@@ -31,7 +35,12 @@ struct fmpnp_ctx {
     int ring_bytes = 0;   // 0 = automatic (see geometry())
     int depth = 0;
     int ctas_per_sm = 0;
+    int cluster = 0;
     int smem_configured = -1;
+    int nonportable = -1;
+    int experiment = 0;
+    int direct_max_c = 256;
+    Geometry_last last = {0, 0, 0, 0};
     int64_t launches = 0;
 };
 
@@ -136,40 +145,72 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
     return FMPNP_SUCCESS;
 }
 
-// Launch geometry.  Batches that fill the GPU run 2 CTAs per SM with a 96 KB staging ring each
-// (measured best: 0.97 of the HBM copy peak at B >= 296).  Batches of at most one query per SM
-// cannot use the second CTA slot, so each CTA takes the whole shared memory instead (200 KB ring,
-// 3 slots per consumer warp: 0.85 instead of 0.62 of peak at B = 148).  FMPNP_RING_KB /
-// FMPNP_DEPTH / FMPNP_CTAS_PER_SM override the choice (tuning only).
-int geometry(fmpnp_ctx* ctx, int32_t B, int* grid, int* ring_bytes, int* depth, int* slot_bytes) {
+// Launch geometry.
+//   * Batches that fill the GPU (B > 148): one CTA per query, 2 CTAs per SM, a 96 KB staging ring each
+//     (measured 0.95 of the HBM copy peak at B = 256).
+//   * Smaller batches: a thread-block cluster of 2..16 CTAs refines each query together (the points are
+//     split, the normal equations combined through distributed shared memory), so that all SMs stream
+//     even for a single query; when that still leaves at most one CTA per SM each CTA takes the whole
+//     shared memory as its ring.
+// FMPNP_RING_KB / FMPNP_MIN_DEPTH / FMPNP_CTAS_PER_SM / FMPNP_CLUSTER override the choice (tuning only).
+struct Geometry {
+    int grid, ring_bytes, ring_per_warp, min_depth, cluster;
+};
+
+int geometry(fmpnp_ctx* ctx, int32_t B, int requested_cluster, Geometry* g) {
     int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
+    int S = requested_cluster > 0 ? requested_cluster : ctx->cluster;
     const int static_b = (int)refine_static_smem_bytes();
     const int budget = ctx->max_smem_optin - static_b - 1024;
-    if (per_sm <= 0) per_sm = (B <= ctx->sm_count) ? 1 : 2;
-    if (per_sm > 2) per_sm = 2;
-    if (ring <= 0) ring = (per_sm == 1) ? budget : 96 * 1024;
-    if (d <= 0) d = (per_sm == 1) ? 3 : 2;
-    if (d < 2) d = 2;
-    if (d > kMaxDepth) d = kMaxDepth;
-    if (ring > budget) ring = budget;
-    int slot = (ring / (kConsumerWarps * d)) & ~127;
-    if (slot < 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", ring);
-    ring = slot * kConsumerWarps * d;
-    if (ctx->smem_configured < ring) {
-        FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(ring));
-        ctx->smem_configured = ring;
+    if (S != 0 && S != 1 && S != 2 && S != 4 && S != 8 && S != 16)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "cluster_size must be 0 (auto), 1, 2, 4, 8 or 16; got %d", S);
+    const bool auto_cluster = S == 0;
+    if (auto_cluster) {
+        S = 1;
+        while (S < 16 && (int64_t)B * S * 2 <= 2 * (int64_t)ctx->sm_count) S *= 2;
     }
-    int g = ctx->sm_count * per_sm;
-    if (g > B) g = B;
-    if (g < 1) g = 1;
-    *grid = g;
-    *ring_bytes = ring;
-    *depth = d;
-    *slot_bytes = slot;
-    return FMPNP_SUCCESS;
+    if (d <= 0) d = 2;
+    if (d > kMaxDepth) d = kMaxDepth;
+    for (;;) {
+        int ps = per_sm > 0 ? (per_sm > 2 ? 2 : per_sm) : (((int64_t)B * S <= ctx->sm_count) ? 1 : 2);
+        int r = ring > 0 ? ring : (ps == 1 ? budget : 96 * 1024);
+        if (r > budget) r = budget;
+        if (r < 64 * 1024) r = 64 * 1024;  // the reductions use the ring as scratch (28 x 288 doubles)
+        const int per_warp = (r / kConsumerWarps) & ~127;
+        if (per_warp < 2 * 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", r);
+        r = per_warp * kConsumerWarps;
+        if (ctx->smem_configured < r) {
+            FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(r));
+            ctx->smem_configured = r;
+        }
+        int clusters = ctx->sm_count * ps / S;
+        const int want_np = S > 8 ? 1 : 0;
+        if (ctx->nonportable != want_np) {
+            FMPNP_CUDA(ctx, refine_allow_nonportable_clusters(want_np));
+            ctx->nonportable = want_np;
+        }
+        if (S > 1) {
+            const int fit = max_active_clusters(S, r);
+            if (fit < 1) {  // such a cluster cannot be scheduled: halve it
+                if (!auto_cluster && S == requested_cluster)
+                    return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "a cluster of %d CTAs with %d B of shared memory cannot be scheduled", S, r);
+                S /= 2;
+                continue;
+            }
+            if (clusters > fit) clusters = fit;
+        }
+        if (clusters > B) clusters = B;
+        if (clusters < 1) clusters = 1;
+        g->grid = clusters * S;
+        g->ring_bytes = r;
+        g->ring_per_warp = per_warp;
+        g->min_depth = d;
+        g->cluster = S;
+        return FMPNP_SUCCESS;
+    }
 }
 
-void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, int depth, int slot_bytes) {
+void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, const Geometry& g) {
     memset(&lp, 0, sizeof(lp));
     lp.queries = ctx->d_queries;
     lp.B = B;
@@ -177,8 +218,11 @@ void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, int
     lp.supp = ctx->d_supp;
     lp.n_max = n_max;
     lp.work_counter = ctx->d_counter;
-    lp.depth = depth;
-    lp.slot_bytes = slot_bytes;
+    lp.ring_per_warp = g.ring_per_warp;
+    lp.min_depth = g.min_depth;
+    lp.cluster_size = g.cluster;
+    lp.experiment = ctx->experiment;
+    lp.direct_max_c = ctx->direct_max_c;
 }
 
 }  // namespace
@@ -215,7 +259,10 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
         return FMPNP_ERR_CUDA;
     }
     ctx->ring_bytes = env_int("FMPNP_RING_KB", 0) * 1024;
-    ctx->depth = env_int("FMPNP_DEPTH", 0);
+    ctx->depth = env_int("FMPNP_MIN_DEPTH", 0);
+    ctx->cluster = env_int("FMPNP_CLUSTER", 0);
+    ctx->experiment = env_int("FMPNP_EXPERIMENT", 0);
+    ctx->direct_max_c = env_int("FMPNP_DIRECT_MAX_C", 256);
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     *out = ctx;
     return FMPNP_SUCCESS;
@@ -239,6 +286,14 @@ const char* fmpnp_last_error(const fmpnp_ctx* ctx) { return ctx ? ctx->err : "nu
 
 int64_t fmpnp_launch_count(const fmpnp_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+int fmpnp_last_geometry(const fmpnp_ctx* ctx, int32_t* grid, int32_t* cluster_size, int32_t* ring_bytes) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (grid) *grid = ctx->last.grid;
+    if (cluster_size) *cluster_size = ctx->last.cluster;
+    if (ring_bytes) *ring_bytes = ctx->last.ring_bytes;
+    return FMPNP_SUCCESS;
+}
+
 int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, const fmpnp_options* o,
                        fmpnp_result* results, const fmpnp_history* hist, void* stream_) {
     if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
@@ -261,11 +316,11 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
-    int grid, ring, depth, slot;
-    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    Geometry g;
+    int rc = geometry(ctx, B, o->cluster_size, &g);
     if (rc) return rc;
     int32_t n_max;
-    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    rc = stage(ctx, probs, B, g.grid, &n_max, stream);
     if (rc) return rc;
     const int levels_eff = o->n_levels > 0 ? o->n_levels : 1;
     if (hist) {
@@ -275,7 +330,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
                         hist->n_stride);
     }
     LaunchParams lp;
-    fill_common(lp, ctx, B, n_max, depth, slot);
+    fill_common(lp, ctx, B, n_max, g);
     lp.mode = kModeRefine;
     lp.n_iters = o->n_iters;
     lp.loss_id = o->loss_id;
@@ -300,8 +355,9 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
         lp.hist.kept = hist->kept;
     }
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
-    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
     ctx->launches += 1;
+    ctx->last = {g.grid, g.cluster, g.ring_bytes, 0};
     return FMPNP_SUCCESS;
 }
 
@@ -316,22 +372,23 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
-    int grid, ring, depth, slot;
-    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    Geometry g;
+    int rc = geometry(ctx, B, 0, &g);
     if (rc) return rc;
     int32_t n_max;
-    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    rc = stage(ctx, probs, B, g.grid, &n_max, stream);
     if (rc) return rc;
     LaunchParams lp;
-    fill_common(lp, ctx, B, n_max, depth, slot);
+    fill_common(lp, ctx, B, n_max, g);
     lp.mode = kModeComputeCost;
     lp.use_ratio = std::isnan(o->ratio_threshold) ? 0 : 1;
     lp.ratio_thr = lp.use_ratio ? o->ratio_threshold : 0.0;
     lp.cost_out = costs;
     lp.nsup_out = n_supported;
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
-    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
     ctx->launches += 1;
+    ctx->last = {g.grid, g.cluster, g.ring_bytes, 0};
     return FMPNP_SUCCESS;
 }
 
@@ -349,14 +406,14 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
-    int grid, ring, depth, slot;
-    int rc = geometry(ctx, B, &grid, &ring, &depth, &slot);
+    Geometry g;
+    int rc = geometry(ctx, B, 0, &g);
     if (rc) return rc;
     int32_t n_max;
-    rc = stage(ctx, probs, B, grid, &n_max, stream);
+    rc = stage(ctx, probs, B, g.grid, &n_max, stream);
     if (rc) return rc;
     LaunchParams lp;
-    fill_common(lp, ctx, B, n_max, depth, slot);
+    fill_common(lp, ctx, B, n_max, g);
     lp.mode = kModeFindInliers;
     lp.loss_id = loss_id;
     lp.alpha = barron_alpha;
@@ -365,8 +422,9 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     lp.inliers_out = inliers;
     lp.inliers_stride = n_stride;
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
-    FMPNP_CUDA(ctx, launch_refine(lp, grid, ring, stream));
+    FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
     ctx->launches += 1;
+    ctx->last = {g.grid, g.cluster, g.ring_bytes, 0};
     return FMPNP_SUCCESS;
 }
 

@@ -25,8 +25,12 @@
 #include <cmath>
 #include <cstdint>
 
+#include <cooperative_groups.h>
+
 #include "fmpnp_device.cuh"
 #include "fmpnp_kernels.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace fmpnp {
 
@@ -39,9 +43,14 @@ struct __align__(16) Shared {
     double ev[28];        // last evaluation: H (21), g (6), sum of rho
     double A[36], b[8];   // solver workspace
     double red[kWarps][32];
+    double tree[5][32];   // pairwise-tree stack over this CTA's point ranges
+    double climit;
+    double cpart[2][32];  // this CTA's partial sums, read by the other CTAs of the cluster (double-buffered)
     double prev_cost, best_cost, lambda, lr, ev_cost, limit, initial_cost;
     long long gathered;
     int32_t red_i[kWarps][4];
+    int32_t cpart_i[2][4];
+    int32_t climit_nan;
     int32_t ev_count, ev_nsup, best_n, has_best, status, flag, hist_len, query, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
     // --- staging ring
@@ -51,14 +60,18 @@ struct __align__(16) Shared {
     int32_t cellbuf[32];
 };
 
+// Position inside a consumer warp's sub-ring.  The mbarriers of slot i are full[w * kMaxDepth + i]
+// and empty[w * kMaxDepth + i] whatever the current ring depth is, and bit i of `bits` is the phase
+// parity of that slot's next use.  The ring is empty between evaluations, so an evaluation with a
+// different depth simply starts again at slot 0 and keeps the per-slot parities.
 struct RingPos {
-    int32_t pos;     // slot inside the sub-ring
-    uint32_t phase;  // mbarrier phase parity of that slot's current use
+    int32_t pos;    // slot inside the sub-ring
+    uint32_t bits;  // per-slot mbarrier phase parity
+    int32_t cpar;   // which half of Shared::cpart the next cluster reduction uses
+    __device__ __forceinline__ uint32_t phase() const { return (bits >> pos) & 1u; }
     __device__ __forceinline__ void advance(int depth) {
-        if (++pos == depth) {
-            pos = 0;
-            phase ^= 1u;
-        }
+        bits ^= 1u << pos;
+        if (++pos == depth) pos = 0;
     }
 };
 
@@ -77,8 +90,39 @@ struct EvalCtx {
     uint8_t* h_kept;
     uint8_t* inl_out;      // find_inliers output (or null)
     unsigned char* ring;
-    int32_t depth, slot_bytes;
+    int32_t ring_per_warp, min_depth;  // launch geometry: bytes of staging ring per consumer warp
+    int32_t depth, slot_bytes;         // per-evaluation geometry (set_geometry)
+    int32_t CH, nCh;                   // channels per staged item, items per point
+    int32_t n0, n1;                    // this CTA's share of the points: [n0, n1)
+    int32_t range_len;                 // points per fixed reduction range (kRanges ranges cover N)
+    int32_t csize, crank;              // thread-block cluster working on this query
+    int32_t experiment;
+    int32_t direct_max_c;              // slices up to this many channels are loaded directly (no staging)
 };
+
+// Staging geometry of one evaluation.  An item is one point x CH channels x ROWS rows; a whole
+// point when it fits `min_depth` times into the warp's sub-ring (short rows then get a deeper
+// ring, up to kMaxDepth slots, so the bytes in flight stay the same), else equal chunks of a
+// multiple of 32 channels.
+__device__ __forceinline__ void set_geometry(EvalCtx& c, int rows) {
+    const int W = c.ring_per_warp;
+    const int full = rows * c.Cl * 4;
+    if (((full + 127) & ~127) * c.min_depth <= W) {
+        c.CH = c.Cl;
+        c.nCh = 1;
+    } else {
+        // chunks of a multiple of 128 channels keep the lane <-> channel mapping (and so the rounding
+        // of the per-point sums) independent of the ring geometry
+        int maxCH = ((W / c.min_depth) / (rows * 4)) & ~127;
+        if (maxCH < 128) maxCH = 128;
+        c.nCh = (c.Cl + maxCH - 1) / maxCH;
+        const int per = (c.Cl + c.nCh - 1) / c.nCh;
+        c.CH = min(maxCH, (per + 127) & ~127);
+        c.nCh = (c.Cl + c.CH - 1) / c.CH;
+    }
+    c.slot_bytes = (rows * c.CH * 4 + 127) & ~127;
+    c.depth = min(kMaxDepth, W / c.slot_bytes);
+}
 
 // ---------------------------------------------------------------------------------------------
 // channel accumulation: c += e^2, Sxx += gx^2, Sxy += gx gy, Syy += gy^2, bx += gx e, by += gy e
@@ -156,6 +200,87 @@ __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const doub
 }
 
 // ---------------------------------------------------------------------------------------------
+// Direct streaming for short rows (slices of at most `direct_max_c` channels): staging a 512-byte
+// row through TMA + mbarriers costs more than the row itself, so here every warp projects its own
+// 32 points and loads the rows straight into registers.  L = 32 / G lanes share one point (each
+// lane KB float4 of every row per pass), G points are in flight per warp, and the channel sums
+// are reduced over the L lanes only.  The lane <-> channel mapping depends on the slice length
+// alone, never on the launch geometry.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p));
+    return v;
+}
+
+template <bool GRAD, int KB>
+__device__ void stream_points_direct(const EvalCtx& c, const double* R, const double* t) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const QueryDev& q = *c.q;
+    const int nvec = c.Cl >> 2;  // float4 per row
+    int L = 1;
+    while (L < 32 && L * KB < nvec) L <<= 1;
+    const int G = 32 / L;
+    const int sg = lane / L, sl = lane % L;
+    const int N = c.n1;
+    for (int base = c.n0 + warp * 32; base < N; base += kWarps * 32) {
+        const int n = base + lane;
+        int cell = -1;
+        if (n < N) cell = project_and_flag(c, R, t, n);
+        unsigned mask = __ballot_sync(0xffffffffu, cell >= 0);
+        while (mask) {
+            const unsigned j = __fns(mask, 0, sg + 1);  // the sg-th supported point still to do
+            const bool act = j != 0xffffffffu;
+            const int cj = __shfl_sync(0xffffffffu, cell, act ? (int)j : 0);
+            const int nj = base + (int)j;
+            double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            if (act) {
+                const float4* pF = reinterpret_cast<const float4*>(q.F + (size_t)cj * q.C + c.c0);
+                const float4* pR = reinterpret_cast<const float4*>(q.ref + (size_t)nj * q.C + c.c0);
+                const float4* pGx = GRAD ? reinterpret_cast<const float4*>(q.Gx + (size_t)cj * q.C + c.c0) : nullptr;
+                const float4* pGy = GRAD ? reinterpret_cast<const float4*>(q.Gy + (size_t)cj * q.C + c.c0) : nullptr;
+                for (int v0 = sl; v0 < nvec; v0 += L * KB) {
+                    float4 f[KB], r[KB], gx[KB], gy[KB];
+#pragma unroll
+                    for (int k = 0; k < KB; ++k) {
+                        const int v = v0 + k * L;
+                        const bool in = v < nvec;
+                        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                        f[k] = in ? ldg_stream(pF + v) : z;
+                        r[k] = in ? ldg_stream(pR + v) : z;
+                        gx[k] = (GRAD && in) ? ldg_stream(pGx + v) : z;
+                        gy[k] = (GRAD && in) ? ldg_stream(pGy + v) : z;
+                    }
+#pragma unroll
+                    for (int k = 0; k < KB; ++k) {
+                        acc1<GRAD>(f[k].x, r[k].x, gx[k].x, gy[k].x, a);
+                        acc1<GRAD>(f[k].y, r[k].y, gx[k].y, gy[k].y, a);
+                        acc1<GRAD>(f[k].z, r[k].z, gx[k].z, gy[k].z, a);
+                        acc1<GRAD>(f[k].w, r[k].w, gx[k].w, gy[k].w, a);
+                    }
+                }
+            }
+            constexpr int NV = GRAD ? 6 : 1;
+            for (int off = L >> 1; off > 0; off >>= 1) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) a[i] = __dadd_rn(a[i], shfl_xor_f64(a[i], off));
+            }
+            if (act && sl == 0) {
+                double2* o = reinterpret_cast<double2*>(c.rec + (size_t)nj * kRecDoubles);
+                o[0] = make_double2(a[0], a[1]);
+                if (GRAD) {
+                    o[1] = make_double2(a[2], a[3]);
+                    o[2] = make_double2(a[4], a[5]);
+                }
+            }
+            for (int g = 0; g < G && mask; ++g) mask &= mask - 1;  // drop the G points just done
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Streaming phase: one record per supported point.
 // ---------------------------------------------------------------------------------------------
 template <bool GRAD>
@@ -163,13 +288,10 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const QueryDev& q = *c.q;
     constexpr int ROWS = GRAD ? 4 : 2;
-    const int N = q.N;
+    const int N = c.n1;
 
     if (c.aligned) {
-        // channels per staged item: whole slice if it fits a slot, else chunks (multiples of 128 when possible)
-        const int chMax = (c.slot_bytes / (ROWS * 4)) & ~3;
-        const int CH = (c.Cl <= chMax) ? c.Cl : (chMax >= 128 ? (chMax & ~127) : chMax);
-        const int nCh = (c.Cl + CH - 1) / CH;
+        const int CH = c.CH, nCh = c.nCh;
         if (warp == 0) {
             // ---------------- producer: float64 projection + TMA issue.
             // Four lanes serve each consumer warp ("feeder" fw): lane fr issues the bulk copy of row
@@ -179,7 +301,7 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
             constexpr int LPF = 32 / kConsumerWarps;  // lanes per feeder == points per feeder per batch
             static_assert(LPF >= 4, "need one lane per staged row");
             const int fw = lane / LPF, fr = lane % LPF;
-            for (int base = 0; base < N; base += 32) {
+            for (int base = c.n0; base < N; base += 32) {
                 const int n = base + lane;
                 int cell = -1;
                 if (n < N) cell = project_and_flag(c, R, t, n);
@@ -190,15 +312,16 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
                     while (jj < LPF && sh.cellbuf[fw + kConsumerWarps * jj] < 0) ++jj;  // next supported point
                     const bool have = jj < LPF;
                     if (!__any_sync(0xffffffffu, have)) break;
-                    const int slot = fw * c.depth + rp.pos;
-                    const bool go = have && mbar_test(&sh.empty[slot], rp.phase ^ 1u);
+                    const int slot = fw * c.depth + rp.pos;    // staging memory
+                    const int bar = fw * kMaxDepth + rp.pos;   // its barriers / meta
+                    const bool go = have && mbar_test(&sh.empty[bar], rp.phase() ^ 1u);
                     const int j = fw + kConsumerWarps * (have ? jj : 0);
                     const int cj = sh.cellbuf[j], nj = base + j;
                     const int off = ch * CH;
                     const uint32_t rowB = (uint32_t)min(CH, c.Cl - off) * 4u;
                     if (go && fr == 0) {
-                        sh.meta[slot] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
-                        mbar_arrive_expect_tx(&sh.full[slot], (uint32_t)ROWS * rowB);
+                        sh.meta[bar] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
+                        mbar_arrive_expect_tx(&sh.full[bar], (uint32_t)ROWS * rowB);
                     }
                     __syncwarp();
                     if (go && fr < ROWS) {
@@ -208,7 +331,7 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
                         else
                             src = (fr == 0 ? q.F : (fr == 1 ? q.Gx : q.Gy)) + (size_t)cj * q.C;
                         tma_bulk_g2s(c.ring + (size_t)slot * c.slot_bytes + fr * rowB, src + c.c0 + off, rowB,
-                                     &sh.full[slot]);
+                                     &sh.full[bar]);
                     }
                     if (go) {
                         rp.advance(c.depth);
@@ -225,11 +348,11 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
                 bool posted = false;
                 for (;;) {
                     if (!posted) {
-                        const int slot = fw * c.depth + rp.pos;
-                        if (mbar_test(&sh.empty[slot], rp.phase ^ 1u)) {
+                        const int bar = fw * kMaxDepth + rp.pos;
+                        if (mbar_test(&sh.empty[bar], rp.phase() ^ 1u)) {
                             if (fr == 0) {
-                                sh.meta[slot] = make_int2(-1, 0);
-                                mbar_arrive(&sh.full[slot]);
+                                sh.meta[bar] = make_int2(-1, 0);
+                                mbar_arrive(&sh.full[bar]);
                             }
                             rp.advance(c.depth);
                             posted = true;
@@ -244,13 +367,13 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
             const int w = warp - 1;
             double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
             for (;;) {
-                const int slot = w * c.depth + rp.pos;
-                mbar_wait(&sh.full[slot], rp.phase);
-                const int2 m = sh.meta[slot];
+                const int slot = w * c.depth + rp.pos, bar = w * kMaxDepth + rp.pos;
+                mbar_wait(&sh.full[bar], rp.phase());
+                const int2 m = sh.meta[bar];
                 rp.advance(c.depth);
                 if (m.x < 0) {
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&sh.empty[slot]);
+                    if (lane == 0) mbar_arrive(&sh.empty[bar]);
                     break;
                 }
                 const int ch = m.y & 0xffff;
@@ -261,13 +384,13 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
                 const int cnt = min(CH, c.Cl - ch * CH);
                 accum_slot<GRAD>(c.ring + (size_t)slot * c.slot_bytes, cnt >> 2, lane, a);
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[slot]);  // slot may be refilled
+                if (lane == 0) mbar_arrive(&sh.empty[bar]);  // slot may be refilled
                 if (m.y >> 30) finish_point<GRAD>(a, lane, c.rec + (size_t)m.x * kRecDoubles);
             }
         }
     } else {
         // ---------------- generic path: every warp projects its own 32 points, loads directly
-        for (int base = warp * 32; base < N; base += kWarps * 32) {
+        for (int base = c.n0 + warp * 32; base < N; base += kWarps * 32) {
             const int n = base + lane;
             int cell = -1;
             if (n < N) cell = project_and_flag(c, R, t, n);
@@ -296,52 +419,97 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
 }
 
 // ---------------------------------------------------------------------------------------------
-// Deterministic block reductions (fixed tree: lanes by butterfly, warps in index order)
+// Deterministic reductions.  The points of a query are cut into kRanges fixed ranges (the same for
+// every launch geometry); a range is summed by a fixed tree (threads stride the range, lanes by
+// butterfly, warps in index order) and the range totals are added pairwise, first inside the
+// CTA, then across the cluster.  A CTA owns kRanges / cluster_size consecutive ranges, so the
+// result is bit-identical for every cluster size, batch size and staging-ring geometry.
 // ---------------------------------------------------------------------------------------------
+// Sums v[0..NV) / iv[0..2) over the block through the (idle) staging ring: every thread stores its
+// partials as a column of A[NV][kThreads]; warp w then adds rows w, w + kWarps, ... (each lane 9
+// entries in order, then a butterfly).  Afterwards lane 0 of warp (i % kWarps) holds total i
+// (returned there, 0 elsewhere) and warp 0, lanes 0 / 1 hold the integer totals in `itot`.
+// The caller separates consecutive calls by a __syncthreads().
+constexpr int kSumStride = kThreads;
 template <int NV>
-__device__ __forceinline__ void block_sum(double (&v)[NV], int32_t (&iv)[2], Shared& sh, double* out, int32_t* iout) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+__device__ __forceinline__ void block_sum(double (&v)[NV], int32_t (&iv)[2], Shared& sh, double* scratch,
+                                          double (&tot)[(NV + kWarps - 1) / kWarps], int32_t& itot) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v[i] = __dadd_rn(v[i], shfl_xor_f64(v[i], off));
-    }
+    for (int i = 0; i < NV; ++i) scratch[i * kSumStride + tid] = v[i];
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) iv[i] += __shfl_xor_sync(0xffffffffu, iv[i], off);
     }
-#pragma unroll
-    for (int i = 0; i < NV; ++i)
-        if (lane == i) sh.red[warp][i] = v[i];
     if (lane == 0) {
         sh.red_i[warp][0] = iv[0];
         sh.red_i[warp][1] = iv[1];
     }
     __syncthreads();
-    if (warp == 0) {
-        if (lane < NV) {
-            double s = sh.red[0][lane];
-            for (int w = 1; w < kWarps; ++w) s = __dadd_rn(s, sh.red[w][lane]);
-            out[lane] = s;
+#pragma unroll
+    for (int k = 0; k < (NV + kWarps - 1) / kWarps; ++k) {
+        const int i = warp + k * kWarps;
+        double s = 0.0;
+        if (i < NV) {
+            const double* row = scratch + i * kSumStride + lane;
+            s = row[0];
+#pragma unroll
+            for (int j = 1; j < kWarps; ++j) s = __dadd_rn(s, row[32 * j]);
         }
-        if (lane < 2) {
-            int32_t s = 0;
-            for (int w = 0; w < kWarps; ++w) s += sh.red_i[w][lane];
-            iout[lane] = s;
-        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s = __dadd_rn(s, shfl_xor_f64(s, off));
+        tot[k] = s;
     }
+    itot = 0;
+    if (warp == 0 && lane < 2)
+        for (int w = 0; w < kWarps; ++w) itot += sh.red_i[w][lane];
+}
+
+// Combines the per-CTA values every CTA of the cluster left in its own Shared::cpart[par] /
+// cpart_i[par]: all CTAs read all partials through distributed shared memory and add them in
+// the same pairwise order, so every CTA ends up with bit-identical totals (and then takes the
+// same LM decisions).  One hardware cluster barrier per reduction; the two halves of cpart
+// alternate, so a half is only rewritten after the next barrier, when every CTA has read it.
+template <bool MAX>
+__device__ __forceinline__ void cluster_combine(Shared& sh, int csize, int32_t& par, int nv, double* out, int ni,
+                                                int32_t* iout) {
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    const int tid = threadIdx.x;
+    if (tid < nv) {
+        double v[kRanges];
+#pragma unroll
+        for (int r = 0; r < kRanges; ++r) v[r] = r < csize ? *cl.map_shared_rank(&sh.cpart[par][tid], r) : 0.0;
+#pragma unroll
+        for (int w = 1; w < kRanges; w <<= 1) {
+            if (w < csize) {
+#pragma unroll
+                for (int i = 0; i + w < kRanges; i += 2 * w) v[i] = MAX ? fmax(v[i], v[i + w]) : __dadd_rn(v[i], v[i + w]);
+            }
+        }
+        out[tid] = v[0];
+    } else if (tid >= 32 && tid < 32 + ni) {
+        const int k = tid - 32;
+        int32_t s = 0;
+        for (int r = 0; r < csize; ++r) {
+            const int32_t x = *cl.map_shared_rank(&sh.cpart_i[par][k], r);
+            s = MAX ? (s | x) : (s + x);
+        }
+        iout[k] = s;
+    }
+    par ^= 1;
     __syncthreads();
 }
 
 // ---------------------------------------------------------------------------------------------
-// Per-point phase: robust loss, ratio test, contraction with the projection Jacobian, block sums.
+// Per-point phase: robust loss, ratio test, contraction with the projection Jacobian, sums.
 // Leaves sh.ev[0..27], sh.ev_count (survivors), sh.ev_nsup (supported) and sh.ev_cost (mean rho).
 // ---------------------------------------------------------------------------------------------
 template <bool GRAD>
-__device__ void reduce_points(const EvalCtx& c, const double* R, const double* t, Shared& sh) {
+__device__ void reduce_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     const QueryDev& q = *c.q;
-    const int N = q.N, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const bool use_ratio = c.ratio_mode != 0;
 
@@ -349,7 +517,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         // ratio_threshold_feature_errors (model.py:120-129): limit = max |rho| * threshold
         double m = -INFINITY;
         int nanf = 0;
-        for (int n = tid; n < N; n += kThreads) {
+        for (int n = c.n0 + tid; n < c.n1; n += kThreads) {
             if (!c.supp[n]) continue;
             const double x = __dmul_rn(0.5, c.rec[(size_t)n * kRecDoubles]);
             double rho = x, w = 1.0;
@@ -375,63 +543,124 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
                 mm = fmax(mm, sh.red[w][0]);
                 nf |= sh.red_i[w][0];
             }
-            sh.limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
+            if (c.csize > 1) {
+                sh.cpart[rp.cpar][0] = mm;
+                sh.cpart_i[rp.cpar][0] = nf;
+            } else {
+                sh.limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
+            }
+        }
+        if (c.csize > 1) {
+            cluster_combine<true>(sh, c.csize, rp.cpar, 1, &sh.climit, 1, &sh.climit_nan);
+            if (tid == 0) sh.limit = sh.climit_nan ? NAN : __dmul_rn(sh.climit, c.thr);
         }
         __syncthreads();
     }
     const double limit = use_ratio ? sh.limit : 0.0;
 
-    double acc[28];
-#pragma unroll
-    for (int i = 0; i < 28; ++i) acc[i] = 0.0;
-    int32_t cnt[2] = {0, 0};  // survivors, supported
     const double fx = q.K[0], fy = q.K[4];
-    for (int n = tid; n < N; n += kThreads) {
-        const bool sup = c.supp[n] != 0;
-        bool keep = false;
-        if (sup) {
-            ++cnt[1];
-            const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
-            const double2 r0 = r[0];
-            const double x = __dmul_rn(0.5, r0.x);  // cost = 0.5 * sum e^2 (model.py:338)
-            double rho = x, w = 1.0;
-            if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
-            keep = !use_ratio || (fabs(rho) < limit);
-            if (keep) {
-                ++cnt[0];
-                acc[27] = __dadd_rn(acc[27], rho);
-                if (GRAD) {
-                    const double2 r1 = r[1], r2 = r[2];
-                    const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2], q.im_w,
-                                                  q.im_h);
-                    contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, r0.y, r1.x, r1.y, r2.x, r2.y, acc);
+    int per = c.range_len;                     // points per fixed range
+    int r_first = c.crank * (kRanges / c.csize);
+    int r_count = kRanges / c.csize;
+    if (c.experiment & 1) r_count = 1;  // TEMPORARY experiment: one range per CTA (non-canonical order)
+    int32_t tot_i = 0;  // warp 0, lanes 0 / 1: survivors / supported of this CTA
+    for (int rr = 0; rr < r_count; ++rr) {
+        int r0 = min(q.N, (r_first + rr) * per), r1 = min(q.N, r0 + per);
+        if (c.experiment & 1) {
+            r0 = c.n0;
+            r1 = c.n1;
+        }
+        double acc[28];
+#pragma unroll
+        for (int i = 0; i < 28; ++i) acc[i] = 0.0;
+        int32_t cnt[2] = {0, 0};  // survivors, supported
+        for (int n = r0 + tid; n < r1; n += kThreads) {
+            const bool sup = c.supp[n] != 0;
+            bool keep = false;
+            if (sup) {
+                ++cnt[1];
+                const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+                const double2 rc0 = r[0];
+                const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
+                double rho = x, w = 1.0;
+                if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
+                keep = !use_ratio || (fabs(rho) < limit);
+                if (keep) {
+                    ++cnt[0];
+                    acc[27] = __dadd_rn(acc[27], rho);
+                    if (GRAD) {
+                        const double2 rc1 = r[1], rc2 = r[2];
+                        const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
+                                                      q.im_w, q.im_h);
+                        contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
+                    }
+                }
+            }
+            if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
+            if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
+        }
+        __syncthreads();  // the scratch columns of the previous range have been consumed
+        int32_t it;
+        double tot[4];
+        block_sum<28>(acc, cnt, sh, reinterpret_cast<double*>(c.ring), tot, it);
+        tot_i += it;
+        if (lane == 0) {  // this thread owns totals i = warp + k * kWarps: pairwise tree over the CTA's ranges
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = warp + k * kWarps;
+                if (i >= 28) continue;
+                double x = tot[k];
+                int level = 0;
+                for (int kk = rr; kk & 1; kk >>= 1) {  // binary-counter stack
+                    x = __dadd_rn(sh.tree[level][i], x);
+                    ++level;
+                }
+                sh.tree[level][i] = x;
+                if (rr == r_count - 1) {  // r_count is a power of two: the total sits on top of the stack
+                    if (c.csize > 1)
+                        sh.cpart[rp.cpar][i] = x;
+                    else
+                        sh.ev[i] = x;
                 }
             }
         }
-        if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
-        if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
     }
     int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
-    block_sum<28>(acc, cnt, sh, sh.ev, iout);
+    if (warp == 0 && lane < 2) {
+        if (c.csize > 1)
+            sh.cpart_i[rp.cpar][lane] = tot_i;
+        else
+            iout[lane] = tot_i;
+    }
+    if (c.csize > 1)
+        cluster_combine<false>(sh, c.csize, rp.cpar, 28, sh.ev, 2, iout);
+    else
+        __syncthreads();
     if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;  // mean; 0/0 = NaN like torch's empty mean
+    fence_proxy_async();  // the ring was used as scratch through the generic proxy; TMA writes it next
     __syncthreads();
 }
 
 template <bool GRAD>
-__device__ __forceinline__ void evaluate(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
-    stream_points<GRAD>(c, R, t, sh, rp);
+__device__ __forceinline__ void evaluate(EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+    set_geometry(c, GRAD ? 4 : 2);
+    rp.pos = 0;  // the ring is empty between evaluations; its depth may change with the slice
+    if (c.aligned && c.Cl <= c.direct_max_c)
+        stream_points_direct<GRAD, 4>(c, R, t);
+    else
+        stream_points<GRAD>(c, R, t, sh, rp);
     __syncthreads();
-    reduce_points<GRAD>(c, R, t, sh);
+    reduce_points<GRAD>(c, R, t, sh, rp);
     if (threadIdx.x == 0) {
         sh.n_evals += 1;
         sh.gathered += (long long)sh.ev_nsup * c.Cl * (GRAD ? 4 : 2);
     }
 }
 
-__device__ __forceinline__ bool slice_aligned(const QueryDev& q, int c0, int Cl, bool grad, int slot_bytes) {
+__device__ __forceinline__ bool slice_aligned(const QueryDev& q, int c0, int Cl, bool grad) {
     uintptr_t bits = reinterpret_cast<uintptr_t>(q.F) | reinterpret_cast<uintptr_t>(q.ref);
     if (grad) bits |= reinterpret_cast<uintptr_t>(q.Gx) | reinterpret_cast<uintptr_t>(q.Gy);
-    return (bits & 15u) == 0 && (q.C & 3) == 0 && (c0 & 3) == 0 && (Cl & 3) == 0 && slot_bytes >= 64;
+    return (bits & 15u) == 0 && (q.C & 3) == 0 && (c0 & 3) == 0 && (Cl & 3) == 0;
 }
 
 __device__ __forceinline__ int tri_index(int i, int j) {  // upper triangle, row-major, i <= j
@@ -479,7 +708,7 @@ __device__ void solve_and_update(Shared& sh, int solver, int lane) {
 
 __device__ __forceinline__ void hist_record(const LaunchParams& p, int qi, int e, const double* R, const double* t,
                                             double cost) {
-    if (!p.hist.enabled || e >= p.hist.cap) return;
+    if (!p.hist.enabled || e >= p.hist.cap || (p.cluster_size > 1 && cg::this_cluster().block_rank() != 0)) return;
     const size_t o = (size_t)qi * p.hist.cap + e;
     for (int i = 0; i < 9; ++i) p.hist.Rs[o * 9 + i] = R[i];
     for (int i = 0; i < 3; ++i) p.hist.ts[o * 3 + i] = t[i];
@@ -505,6 +734,11 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     __shared__ Shared sh;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
+    // A query is refined by a thread-block cluster of `csize` CTAs (1 when the batch alone fills the
+    // GPU): each CTA streams a contiguous share of the points, the partial normal equations are
+    // combined through distributed shared memory, and every CTA then takes the same LM decisions.
+    const int csize = p.cluster_size, crank = csize > 1 ? (int)cg::this_cluster().block_rank() : 0;
+    if (csize > 1) cg::this_cluster().sync();  // every CTA of the cluster is resident before any remote access
     if (tid < kConsumerWarps * kMaxDepth) {
         mbar_init(&sh.full[tid], 1);
         mbar_init(&sh.empty[tid], 1);
@@ -513,14 +747,24 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     __syncthreads();
     RingPos rp;
     rp.pos = 0;
-    rp.phase = 0;
+    rp.bits = 0;
+    rp.cpar = 0;
     double* rec = p.rec + (size_t)blockIdx.x * p.n_max * kRecDoubles;
     uint8_t* supp = p.supp + (size_t)blockIdx.x * p.n_max;
 
     for (;;) {
         __syncthreads();
-        if (tid == 0) sh.query = (int32_t)atomicAdd(p.work_counter, 1u);
-        __syncthreads();
+        if (csize > 1) {
+            cg::cluster_group cl = cg::this_cluster();
+            if (crank == 0 && tid == 0) {
+                const int32_t nq = (int32_t)atomicAdd(p.work_counter, 1u);
+                for (int r = 0; r < csize; ++r) *cl.map_shared_rank(&sh.query, r) = nq;
+            }
+            cl.sync();
+        } else {
+            if (tid == 0) sh.query = (int32_t)atomicAdd(p.work_counter, 1u);
+            __syncthreads();
+        }
         const int qi = sh.query;
         if (qi >= p.B) break;
         const QueryDev& q = p.queries[qi];
@@ -530,8 +774,18 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.rec = rec;
         c.supp = supp;
         c.ring = ring;
-        c.depth = p.depth;
-        c.slot_bytes = p.slot_bytes;
+        c.ring_per_warp = p.ring_per_warp;
+        c.min_depth = p.min_depth;
+        c.csize = csize;
+        c.crank = crank;
+        c.experiment = p.experiment;
+        c.direct_max_c = p.direct_max_c;
+        {
+            const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
+            c.range_len = per;
+            c.n0 = min(q.N, crank * (kRanges / csize) * per);
+            c.n1 = min(q.N, (crank + 1) * (kRanges / csize) * per);
+        }
         c.h_px = nullptr;
         c.h_mask = nullptr;
         c.h_kept = nullptr;
@@ -548,14 +802,14 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
             c.c0 = 0;
             c.Cl = q.C;
-            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.aligned = slice_aligned(q, 0, q.C, false);
             c.loss_id = FMPNP_LOSS_SQUARED;
             c.alpha = 0.0;
             c.ratio_mode = p.use_ratio ? 2 : 0;
             c.thr = p.ratio_thr;
             evaluate<false>(c, sh.R, sh.t, sh, rp);
             __syncthreads();
-            if (tid == 0) {
+            if (tid == 0 && crank == 0) {
                 p.cost_out[qi] = sh.ev_nsup > 0 ? sh.ev_cost : NAN;
                 if (p.nsup_out) p.nsup_out[qi] = sh.ev_nsup;
             }
@@ -564,7 +818,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152)
             c.c0 = 0;
             c.Cl = q.C;
-            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.aligned = slice_aligned(q, 0, q.C, false);
             c.loss_id = p.loss_id;
             c.alpha = p.alpha;
             c.ratio_mode = 1;
@@ -592,7 +846,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
             // multilevel_optimization: initial_cost_ = compute_cost(...) on ALL channels (model.py:182)
             c.c0 = 0;
             c.Cl = q.C;
-            c.aligned = slice_aligned(q, 0, q.C, false, p.slot_bytes);
+            c.aligned = slice_aligned(q, 0, q.C, false);
             c.loss_id = FMPNP_LOSS_SQUARED;
             c.alpha = 0.0;
             c.ratio_mode = p.use_ratio ? 2 : 0;
@@ -612,7 +866,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         for (int lvl = 0; run_levels && lvl < nlev; ++lvl) {
             c.c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
             c.Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
-            c.aligned = slice_aligned(q, c.c0, c.Cl, true, p.slot_bytes);
+            c.aligned = slice_aligned(q, c.c0, c.Cl, true);
             c.loss_id = p.loss_id;
             c.alpha = p.alpha;
             c.ratio_mode = p.use_ratio ? 1 : 0;
@@ -708,7 +962,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
             }
             __syncthreads();
         }
-        if (tid == 0) {
+        if (tid == 0 && crank == 0) {
             fmpnp_result& r = p.results[qi];
             for (int i = 0; i < 9; ++i) r.R[i] = sh.R[i];
             for (int i = 0; i < 3; ++i) r.t[i] = sh.t[i];
@@ -773,13 +1027,59 @@ cudaError_t refine_set_max_dynamic_smem(int bytes) {
     return e;
 }
 
-cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream) {
-    switch (p.mode) {
-        case kModeComputeCost: compute_cost_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
-        case kModeFindInliers: find_inliers_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
-        default: refine_kernel<<<grid, kThreads, ring_bytes, stream>>>(p); break;
+// clusters of 16 CTAs (single-query latency mode) are beyond the portable size of 8
+cudaError_t refine_allow_nonportable_clusters(int allow) {
+    cudaError_t e = cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, allow);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(compute_cost_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, allow);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(find_inliers_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, allow);
+    return e;
+}
+
+static void (*kernel_of(int mode))(LaunchParams) {
+    switch (mode) {
+        case kModeComputeCost: return compute_cost_kernel;
+        case kModeFindInliers: return find_inliers_kernel;
+        default: return refine_kernel;
     }
-    return cudaGetLastError();
+}
+
+// grid = clusters x cluster_size CTAs; cluster_size > 1 launches thread-block clusters
+cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = (size_t)ring_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)(p.cluster_size > 1 ? p.cluster_size : 1);
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = p.cluster_size > 1 ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel_of(p.mode), p);
+}
+
+// how many clusters of `cluster_size` CTAs (each with ring_bytes of dynamic shared memory) can be
+// resident at once; 0 if such a cluster cannot be scheduled at all
+int max_active_clusters(int cluster_size, int ring_bytes) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)cluster_size);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = (size_t)ring_bytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)cluster_size;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, refine_kernel, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
 }
 
 }  // namespace fmpnp

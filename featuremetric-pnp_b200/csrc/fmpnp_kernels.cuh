@@ -12,6 +12,7 @@ constexpr int kConsumerWarps = 8;                 // one sub-ring of the shared-
 constexpr int kWarps = kConsumerWarps + 1;        // + 1 producer warp (projection + TMA issue)
 constexpr int kThreads = kWarps * 32;             // 288
 constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
+constexpr int kRanges = 16;                       // fixed reduction ranges per query == max cluster size
 constexpr int kMaxDepth = 8;                      // max slots per sub-ring
 
 enum KernelMode { kModeRefine = 0, kModeComputeCost = 1, kModeFindInliers = 2 };
@@ -59,9 +60,12 @@ struct LaunchParams {
     uint8_t* supp;  // [grid][n_max]
     int32_t n_max;
     unsigned int* work_counter;
-    // staging ring geometry
-    int32_t depth;       // slots per consumer warp
-    int32_t slot_bytes;  // bytes per slot (multiple of 128)
+    // staging ring geometry (slot size / depth are derived per evaluation, see set_geometry)
+    int32_t ring_per_warp;  // bytes of the shared-memory ring owned by one consumer warp
+    int32_t min_depth;      // minimum slots per consumer warp
+    int32_t cluster_size;   // CTAs per query (thread-block cluster); grid = clusters * cluster_size
+    int32_t experiment;
+    int32_t direct_max_c;   // channel slices up to this length are streamed without shared-memory staging
 };
 
 // Host-side launchers (defined in fmpnp_kernels.cu)
@@ -69,6 +73,8 @@ cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaS
 cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, int C, int Hf, int Wf,
                                    cudaStream_t stream);
 size_t refine_static_smem_bytes();
+int max_active_clusters(int cluster_size, int ring_bytes);
+cudaError_t refine_allow_nonportable_clusters(int allow);
 cudaError_t refine_set_max_dynamic_smem(int bytes);
 
 }  // namespace fmpnp

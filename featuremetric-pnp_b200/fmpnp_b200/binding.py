@@ -78,6 +78,9 @@ def lib():
             L.fmpnp_last_error.restype = C.c_char_p
             L.fmpnp_launch_count.argtypes = [C.c_void_p]
             L.fmpnp_launch_count.restype = C.c_int64
+            L.fmpnp_last_geometry.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                              C.POINTER(C.c_int32)]
+            L.fmpnp_last_geometry.restype = C.c_int
             L.fmpnp_refine_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.POINTER(COptions),
                                              C.c_void_p, C.POINTER(CHistory), C.c_void_p]
             L.fmpnp_refine_batch.restype = C.c_int
@@ -126,6 +129,13 @@ class Context:
     @property
     def launches(self):
         return int(lib().fmpnp_launch_count(self._h))
+
+    @property
+    def last_geometry(self):
+        """(CTAs in the grid, CTAs per query, staging-ring bytes per CTA) of the last launch."""
+        g, c, r = C.c_int32(), C.c_int32(), C.c_int32()
+        lib().fmpnp_last_geometry(self._h, C.byref(g), C.byref(c), C.byref(r))
+        return dict(grid=g.value, cluster_size=c.value, ring_bytes=r.value)
 
 
 _default_ctx = {}
@@ -219,8 +229,9 @@ def _problem_array(problems):
     return arr
 
 
-def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None):
+def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None, cluster_size=0):
     o = COptions()
+    o.cluster_size = int(cluster_size)
     lid, alpha = loss_id_of(loss)
     if barron_alpha is not None:
         alpha = float(barron_alpha)
@@ -242,7 +253,7 @@ def _stream_ptr():
 
 
 def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_threshold=None, levels=None,
-                 track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None):
+                 track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None, cluster_size=0):
     """Batched sparseFeaturePnP.forward (levels=None) / multilevel_optimization (levels=[(s, e), ...]).
 
     Returns a dict: `results` (numpy structured array, one fmpnp_result per query, on the host if
@@ -251,7 +262,7 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     ctx = ctx or default_context()
     B = len(problems)
     dev = torch.device("cuda", ctx.device)
-    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha)
+    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size)
     arr = _problem_array(problems)
     res_dev = out if out is not None else torch.empty((max(B, 1), RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
     hist, hbuf = None, None

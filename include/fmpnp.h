@@ -104,7 +104,9 @@ typedef struct {
     int32_t n_levels;       /* 0: forward() on all channels; >0: multilevel_optimization */
     int32_t levels[FMPNP_MAX_LEVELS][2]; /* [start, end) channel slices, in execution order */
     int32_t solver;         /* FMPNP_SOLVER_* */
-    int32_t cluster_size;   /* thread-block cluster per query: 0 = auto, else 1, 2, 4, 8 or 16 */
+    int32_t cluster_size;   /* CTAs (one thread-block cluster) refining each query together:
+                               0 = auto (1 when B fills the GPU, up to 16 for a single query),
+                               else 1, 2, 4, 8 or 16 */
     int32_t reserved[6];
 } fmpnp_options;
 
@@ -177,6 +179,10 @@ int fmpnp_pack_chw_to_hwc(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, f
 
 /* Number of kernels this context has launched so far (bench.py's `gpu_launches`). */
 int64_t fmpnp_launch_count(const fmpnp_ctx *ctx);
+
+/* Launch geometry of the most recent kernel of this context: CTAs in the grid, CTAs per query
+ * (thread-block cluster size) and bytes of shared-memory staging ring per CTA.  Diagnostics. */
+int fmpnp_last_geometry(const fmpnp_ctx *ctx, int32_t *grid, int32_t *cluster_size, int32_t *ring_bytes);
 
 /* sizeof() of the ABI structs (0 problem, 1 options, 2 result, 3 history), so that a binding
  * in another language can verify its mirrors; -1 for an unknown index. */

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     names = set(re.findall(r"\b(fmpnp_[a-z_]+)\s*\(", hdr))
     assert {"fmpnp_create", "fmpnp_destroy", "fmpnp_refine_batch", "fmpnp_compute_cost_batch",
             "fmpnp_find_inliers_batch", "fmpnp_pack_chw_to_hwc", "fmpnp_last_error", "fmpnp_version",
-            "fmpnp_launch_count", "fmpnp_struct_size"} <= names
+            "fmpnp_launch_count", "fmpnp_struct_size", "fmpnp_last_geometry"} <= names
     L = ctypes.CDLL(fm.lib_path())
     for n in names:
         assert hasattr(L, n), "libfmpnp.so does not export " + n

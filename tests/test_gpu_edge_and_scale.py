@@ -117,6 +117,69 @@ def test_more_queries_than_resident_ctas():
 
 
 # ----------------------------------------------------------------------------------------------
+# thread-block clusters: 1..16 CTAs refine one query together (small batches / single queries)
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg", [dict(N=1000, C=256, loss="geman_mcclure_loss", ratio=None, levels=None),
+                                 dict(N=777, C=128, loss="squared_loss", ratio=0.8, levels=None),
+                                 dict(N=3000, C=1024, loss="cauchy_loss", ratio=0.9,
+                                      levels=[(512, 1024), (128, 512), (0, 128)]),
+                                 dict(N=45, C=20, loss="huber_loss", ratio=None, levels=[(8, 20), (0, 8)])])
+def test_cluster_sizes_match_oracle_and_each_other(cfg):
+    """The result does not depend on how many CTAs share a query: the reduction order is fixed
+    (16 point ranges, pairwise tree), so records are bit-identical for cluster sizes 1..16."""
+    sc = synth().make_scene(61, N=cfg["N"], C=cfg["C"], Hf=16, Wf=16, im_width=128, im_height=128,
+                            K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
+                            outlier_frac=0.1)
+    p = to_problem(sc)
+    o = run_oracle(sc, 6, cfg["loss"], 0.01, cfg["ratio"], cfg["levels"])
+    first = None
+    for S in (1, 2, 4, 8, 16):
+        out = fm().refine_batch([p], 6, loss=cfg["loss"], lambda_=0.01, ratio_threshold=cfg["ratio"],
+                                levels=cfg["levels"], track=True, cluster_size=S)
+        g = fm().default_context().last_geometry
+        assert g["cluster_size"] == S and g["grid"] == S, g
+        compare("cluster=%d" % S, out["results"][0], out["history"], o, use_ratio=cfg["ratio"] is not None)
+        if first is None:
+            first = out
+        else:
+            assert same_records(out["results"], first["results"]), "cluster=%d differs from cluster=1" % S
+            for k in ("costs", "Rs", "ts", "points2d", "mask", "kept"):
+                assert np.array_equal(out["history"][k], first["history"][k], equal_nan=k in ("costs", "Rs", "ts")), k
+
+
+def test_automatic_geometry_and_batch_size_independence():
+    """Auto geometry: clusters for small batches, one CTA per query for large ones; the records of a
+    query are bit-identical whatever batch it is part of."""
+    scs = [synth().make_scene(300 + i, N=500, C=1024, Hf=16, Wf=16, im_width=128, im_height=128,
+                              K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
+                              outlier_frac=0.1) for i in range(3)]
+    probs = [to_problem(sc) for sc in scs]
+    ctx = fm().default_context()
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    ref = None
+    for B in (1, 3, 20, 70, sms, sms + 1, 2 * sms + 5):
+        batch = [probs[i % 3] for i in range(B)]
+        r = fm().refine_batch(batch, 5, loss="geman_mcclure_loss", lambda_=0.01)["results"]
+        g = ctx.last_geometry
+        assert g["grid"] % g["cluster_size"] == 0 and g["grid"] <= 2 * sms
+        if B > sms:
+            assert g["cluster_size"] == 1
+        if B == 1:
+            assert g["cluster_size"] >= 8
+            ref = r
+        for i in range(B):
+            assert same_records(r[i], ref[0]) if i % 3 == 0 else True
+        assert same_records(r[:3], r[3:6]) if B >= 6 else True
+    inl = fm().find_inliers_batch(probs, 0.8, loss="cauchy_loss").cpu().numpy()
+    for i, sc in enumerate(scs):
+        inp = sc.reference_inputs()
+        exp = oracle.find_inliers(inp["pts3D"].numpy(), inp["R_init"].numpy(), inp["t_init"].numpy(),
+                                  inp["feature_map_query"].numpy(), inp["feature_ref"].numpy(), inp["K"].numpy(),
+                                  sc.im_width, sc.im_height, 0.8, loss="cauchy_loss")
+        assert np.array_equal(inl[i].astype(bool), exp)
+
+
+# ----------------------------------------------------------------------------------------------
 # exit paths
 # ----------------------------------------------------------------------------------------------
 def test_no_supported_point_returns_initial_pose():
