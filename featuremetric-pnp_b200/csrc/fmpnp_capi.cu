@@ -38,8 +38,6 @@ struct fmpnp_ctx {
     int cluster = 0;
     int smem_configured = -1;
     int nonportable = -1;
-    int experiment = 0;
-    int direct_max_c = 256;
     Geometry_last last = {0, 0, 0, 0};
     int64_t launches = 0;
 };
@@ -176,9 +174,9 @@ int geometry(fmpnp_ctx* ctx, int32_t B, int requested_cluster, Geometry* g) {
         int r = ring > 0 ? ring : (ps == 1 ? budget : 96 * 1024);
         if (r > budget) r = budget;
         if (r < 64 * 1024) r = 64 * 1024;  // the reductions use the ring as scratch (28 x 288 doubles)
-        const int per_warp = (r / kConsumerWarps) & ~127;
+        const int per_warp = (r / kWarps) & ~127;
         if (per_warp < 2 * 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", r);
-        r = per_warp * kConsumerWarps;
+        r = per_warp * kWarps;
         if (ctx->smem_configured < r) {
             FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(r));
             ctx->smem_configured = r;
@@ -221,8 +219,6 @@ void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, con
     lp.ring_per_warp = g.ring_per_warp;
     lp.min_depth = g.min_depth;
     lp.cluster_size = g.cluster;
-    lp.experiment = ctx->experiment;
-    lp.direct_max_c = ctx->direct_max_c;
 }
 
 }  // namespace
@@ -261,8 +257,6 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     ctx->ring_bytes = env_int("FMPNP_RING_KB", 0) * 1024;
     ctx->depth = env_int("FMPNP_MIN_DEPTH", 0);
     ctx->cluster = env_int("FMPNP_CLUSTER", 0);
-    ctx->experiment = env_int("FMPNP_EXPERIMENT", 0);
-    ctx->direct_max_c = env_int("FMPNP_DIRECT_MAX_C", 256);
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     *out = ctx;
     return FMPNP_SUCCESS;

@@ -1,20 +1,24 @@
 // fmpnp_kernels.cu -- the feature-metric PnP refinement as ONE persistent sm_100a kernel.
 //
 // Replaces sparseFeaturePnP.forward / multilevel_optimization / compute_cost and find_inliers
-// of featurePnP/model.py (reference lines cited inline).  One CTA owns one query at a time and
-// runs its whole Levenberg-Marquardt loop on the device: no host synchronisation, no
-// per-iteration launch, no collective.
+// of featurePnP/model.py (reference lines cited inline).  A CTA (or a thread-block cluster of up
+// to 16 CTAs when the batch is small) owns one query at a time and runs its whole
+// Levenberg-Marquardt loop on the device: no host synchronisation, no per-iteration launch,
+// no collective.
 //
 // Per pose evaluation (the only part that touches HBM in bulk):
-//   producer warp   projects 32 points at a time in float64 (bit-exact pixel indices), then 8
-//                   feeder lanes issue TMA bulk copies (cp.async.bulk -> SASS UBLKCP) of the
-//                   channel-contiguous rows F[cell], Gx[cell], Gy[cell], ref[n] into a
-//                   shared-memory ring guarded by mbarriers (one sub-ring per consumer warp);
-//   consumer warps  read the staged rows as float4, accumulate in float64 the per-point
-//                   c = sum e^2, the 2x2 structure tensor S = G^T G and b = G^T e, reduce over
-//                   the channels with warp shuffles and write one 48-byte record per point;
+//   every warp      projects 32 points at a time in float64 (bit-exact pixel indices), then
+//                   streams their channel-contiguous rows F[cell], Gx[cell], Gy[cell], ref[n]
+//                   through its own slice of a shared-memory ring: TMA bulk copies
+//                   (cp.async.bulk -> SASS UBLKCP) signalled on mbarriers, several items in
+//                   flight per warp, the next batch projected while the last rows of the
+//                   current one are still landing.  The staged rows are read as float4 and
+//                   accumulated in float64 into the per-point c = sum e^2, the 2x2 structure
+//                   tensor S = G^T G and b = G^T e; short rows share a warp (L lanes per point),
+//                   long rows are cut into channel chunks.  One 48-byte record per point;
 //   all threads     apply the robust loss / ratio test, contract (S, b) with the 2x6
-//                   projection Jacobian and block-reduce the 6x6 normal equations;
+//                   projection Jacobian and reduce the 6x6 normal equations in a fixed order
+//                   (16 point ranges, pairwise tree: the same bits for any launch geometry);
 //   warp 0          solves the damped system (warp-level Cholesky, pivoted-LU fallback),
 //                   applies the se(3) update and runs the accept / reject / damping schedule.
 // The trial evaluation of iteration i doubles as the linearisation of iteration i+1 when the
@@ -53,26 +57,18 @@ struct __align__(16) Shared {
     int32_t climit_nan;
     int32_t ev_count, ev_nsup, best_n, has_best, status, flag, hist_len, query, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
-    // --- staging ring
-    uint64_t full[kConsumerWarps * kMaxDepth];
-    uint64_t empty[kConsumerWarps * kMaxDepth];
-    int2 meta[kConsumerWarps * kMaxDepth];
-    int32_t cellbuf[32];
+    // --- the supported points of the two batches a warp works on (double-buffered): cell and index
+    int32_t bl_cell[kWarps][2][32];
+    int32_t bl_n[kWarps][2][32];
 };
 
-// Position inside a consumer warp's sub-ring.  The mbarriers of slot i are full[w * kMaxDepth + i]
-// and empty[w * kMaxDepth + i] whatever the current ring depth is, and bit i of `bits` is the phase
-// parity of that slot's next use.  The ring is empty between evaluations, so an evaluation with a
+// Position inside a warp's slice of the ring.  Bit i of `bits` is the phase parity of the next
+// use of slot i's barrier.  The ring is empty between evaluations, so an evaluation with a
 // different depth simply starts again at slot 0 and keeps the per-slot parities.
 struct RingPos {
-    int32_t pos;    // slot inside the sub-ring
+    int32_t pos;    // next slot to consume
     uint32_t bits;  // per-slot mbarrier phase parity
     int32_t cpar;   // which half of Shared::cpart the next cluster reduction uses
-    __device__ __forceinline__ uint32_t phase() const { return (bits >> pos) & 1u; }
-    __device__ __forceinline__ void advance(int depth) {
-        bits ^= 1u << pos;
-        if (++pos == depth) pos = 0;
-    }
 };
 
 struct EvalCtx {
@@ -90,38 +86,43 @@ struct EvalCtx {
     uint8_t* h_kept;
     uint8_t* inl_out;      // find_inliers output (or null)
     unsigned char* ring;
-    int32_t ring_per_warp, min_depth;  // launch geometry: bytes of staging ring per consumer warp
+    int32_t ring_per_warp, min_depth;  // launch geometry: bytes of staging ring per warp
     int32_t depth, slot_bytes;         // per-evaluation geometry (set_geometry)
     int32_t CH, nCh;                   // channels per staged item, items per point
+    int32_t L;                         // lanes sharing one point when a whole point is one item (nCh == 1)
     int32_t n0, n1;                    // this CTA's share of the points: [n0, n1)
     int32_t range_len;                 // points per fixed reduction range (kRanges ranges cover N)
     int32_t csize, crank;              // thread-block cluster working on this query
-    int32_t experiment;
-    int32_t direct_max_c;              // slices up to this many channels are loaded directly (no staging)
 };
 
-// Staging geometry of one evaluation.  An item is one point x CH channels x ROWS rows; a whole
-// point when it fits `min_depth` times into the warp's sub-ring (short rows then get a deeper
-// ring, up to kMaxDepth slots, so the bytes in flight stay the same), else equal chunks of a
-// multiple of 32 channels.
+// Staging geometry of one evaluation.
+//   * Short rows: L = max(4, next power of two >= Cl / 8) lanes share a point (2 float4 of every
+//     row per lane and pass), an item is the 32 / L points a warp accumulates together.
+//   * Rows of more than 256 channels: the whole warp works on one point; the point is one item
+//     if `min_depth` of them fit the warp's ring slice, else it is cut into equal chunks of a
+//     multiple of 128 channels.
+// The lane <-> channel mapping (and so the rounding of the per-point sums) depends on the slice
+// length only, never on the ring size: results are bit-identical for every launch geometry.
 __device__ __forceinline__ void set_geometry(EvalCtx& c, int rows) {
     const int W = c.ring_per_warp;
-    const int full = rows * c.Cl * 4;
-    if (((full + 127) & ~127) * c.min_depth <= W) {
-        c.CH = c.Cl;
-        c.nCh = 1;
-    } else {
-        // chunks of a multiple of 128 channels keep the lane <-> channel mapping (and so the rounding
-        // of the per-point sums) independent of the ring geometry
+    const int nvec = c.Cl >> 2;
+    int L = 4;
+    while (L < 32 && L * 2 < nvec) L <<= 1;
+    c.L = L;
+    c.CH = c.Cl;
+    c.nCh = 1;
+    int item = (32 / L) * rows * c.Cl * 4;
+    if (L == 32 && ((item + 127) & ~127) * c.min_depth > W) {
         int maxCH = ((W / c.min_depth) / (rows * 4)) & ~127;
         if (maxCH < 128) maxCH = 128;
         c.nCh = (c.Cl + maxCH - 1) / maxCH;
         const int per = (c.Cl + c.nCh - 1) / c.nCh;
         c.CH = min(maxCH, (per + 127) & ~127);
         c.nCh = (c.Cl + c.CH - 1) / c.CH;
+        item = rows * c.CH * 4;
     }
-    c.slot_bytes = (rows * c.CH * 4 + 127) & ~127;
-    c.depth = min(kMaxDepth, W / c.slot_bytes);
+    c.slot_bytes = (item + 127) & ~127;
+    c.depth = max(1, min(kMaxDepth, W / c.slot_bytes));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -142,47 +143,6 @@ __device__ __forceinline__ void acc1(float f, float r, float gx, float gy, doubl
     }
 }
 
-// staged rows in a slot: GRAD ? [F | Gx | Gy | ref] : [F | ref], each `nvec` float4 long
-template <bool GRAD>
-__device__ __forceinline__ void accum_slot(const unsigned char* slot, int nvec, int lane, double (&a)[6]) {
-    const float4* pF = reinterpret_cast<const float4*>(slot);
-    const float4* pGx = pF + nvec;
-    const float4* pGy = pF + 2 * nvec;
-    const float4* pR = pF + (GRAD ? 3 : 1) * nvec;
-#pragma unroll 2
-    for (int v = lane; v < nvec; v += 32) {
-        const float4 f = pF[v];
-        const float4 r = pR[v];
-        float4 gx = make_float4(0.f, 0.f, 0.f, 0.f), gy = gx;
-        if (GRAD) {
-            gx = pGx[v];
-            gy = pGy[v];
-        }
-        acc1<GRAD>(f.x, r.x, gx.x, gy.x, a);
-        acc1<GRAD>(f.y, r.y, gx.y, gy.y, a);
-        acc1<GRAD>(f.z, r.z, gx.z, gy.z, a);
-        acc1<GRAD>(f.w, r.w, gx.w, gy.w, a);
-    }
-}
-
-template <bool GRAD>
-__device__ __forceinline__ void finish_point(double (&a)[6], int lane, double* rec_n) {
-    constexpr int NV = GRAD ? 6 : 1;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) a[i] = __dadd_rn(a[i], shfl_xor_f64(a[i], off));
-    }
-    if (lane == 0) {
-        double2* o = reinterpret_cast<double2*>(rec_n);
-        o[0] = make_double2(a[0], a[1]);
-        if (GRAD) {
-            o[1] = make_double2(a[2], a[3]);
-            o[2] = make_double2(a[4], a[5]);
-        }
-    }
-}
-
 // projects point n, records support / history, returns the feature-map cell or -1
 __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const double* R, const double* t, int n) {
     const QueryDev& q = *c.q;
@@ -200,195 +160,222 @@ __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const doub
 }
 
 // ---------------------------------------------------------------------------------------------
-// Direct streaming for short rows (slices of at most `direct_max_c` channels): staging a 512-byte
-// row through TMA + mbarriers costs more than the row itself, so here every warp projects its own
-// 32 points and loads the rows straight into registers.  L = 32 / G lanes share one point (each
-// lane KB float4 of every row per pass), G points are in flight per warp, and the channel sums
-// are reduced over the L lanes only.  The lane <-> channel mapping depends on the slice length
-// alone, never on the launch geometry.
+// Staged streaming (16-byte aligned slices).  Every warp is its own producer and consumer: it
+// copies the rows of its next items into its slice of the shared-memory ring with cp.async
+// (SASS LDGSTS.BYPASS.128: L2 -> shared memory, no registers, one commit group per item) and
+// accumulates the oldest item once it has landed.  LOG2L = log2 of the lanes sharing one point.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float4 ldg_stream(const float4* p) {
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "l"(p));
-    return v;
+template <bool GRAD, int LOG2L>
+__device__ __forceinline__ void reduce_lanes(double (&a)[6]) {
+    constexpr int NV = GRAD ? 6 : 1;
+#pragma unroll
+    for (int s = LOG2L - 1; s >= 0; --s) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) a[i] = __dadd_rn(a[i], shfl_xor_f64(a[i], 1 << s));
+    }
 }
 
-template <bool GRAD, int KB>
-__device__ void stream_points_direct(const EvalCtx& c, const double* R, const double* t) {
+template <bool GRAD>
+__device__ __forceinline__ void write_record(const double (&a)[6], double* rec_n) {
+    double2* o = reinterpret_cast<double2*>(rec_n);
+    o[0] = make_double2(a[0], a[1]);
+    if (GRAD) {
+        o[1] = make_double2(a[2], a[3]);
+        o[2] = make_double2(a[4], a[5]);
+    }
+}
+
+template <bool GRAD>
+__device__ __forceinline__ void acc4(uint32_t aF, uint32_t aGx, uint32_t aGy, uint32_t aR, double (&a)[6]) {
+    const float4 f = lds128(aF), r = lds128(aR);
+    float4 gx = make_float4(0.f, 0.f, 0.f, 0.f), gy = gx;
+    if (GRAD) {
+        gx = lds128(aGx);
+        gy = lds128(aGy);
+    }
+    acc1<GRAD>(f.x, r.x, gx.x, gy.x, a);
+    acc1<GRAD>(f.y, r.y, gx.y, gy.y, a);
+    acc1<GRAD>(f.z, r.z, gx.z, gy.z, a);
+    acc1<GRAD>(f.w, r.w, gx.w, gy.w, a);
+}
+
+template <bool GRAD, int LOG2L>
+__device__ void stream_staged(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+    constexpr int ROWS = GRAD ? 4 : 2;
+    constexpr int L = 1 << LOG2L, G = 32 / L;
+    constexpr bool SHORT = LOG2L < 5;  // several points per item, at most 2 float4 of a row per lane
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const QueryDev& q = *c.q;
-    const int nvec = c.Cl >> 2;  // float4 per row
-    int L = 1;
-    while (L < 32 && L * KB < nvec) L <<= 1;
-    const int G = 32 / L;
-    const int sg = lane / L, sl = lane % L;
     const int N = c.n1;
-    for (int base = c.n0 + warp * 32; base < N; base += kWarps * 32) {
-        const int n = base + lane;
+    const int CH = c.CH, nCh = c.nCh, depth = c.depth, Cl = c.Cl;
+    const uint32_t ring = smem_u32(c.ring) + (uint32_t)(warp * c.ring_per_warp);
+    const uint32_t slot_bytes = (uint32_t)c.slot_bytes;
+    const int32_t* bcell = &sh.bl_cell[warp][0][0];  // [2][32]
+    const int32_t* bn = &sh.bl_n[warp][0][0];
+    // batches of 32 points owned by this warp: base = n0 + (warp + b * kWarps) * 32
+    const int first = c.n0 + warp * 32;
+    const int nb = first < N ? (N - first + kWarps * 32 - 1) / (kWarps * 32) : 0;
+    if (nb == 0) return;
+
+    // row base pointers with this lane's 16-byte piece folded in
+    const char* baseF = reinterpret_cast<const char*>(q.F + c.c0) + lane * 16;
+    const char* baseGx = GRAD ? reinterpret_cast<const char*>(q.Gx + c.c0) + lane * 16 : nullptr;
+    const char* baseGy = GRAD ? reinterpret_cast<const char*>(q.Gy + c.c0) + lane * 16 : nullptr;
+    const char* baseR = reinterpret_cast<const char*>(q.ref + c.c0) + lane * 16;
+    const uint32_t pitch = (uint32_t)q.C * 4u;  // bytes between rows of a map / of ref
+
+    // projects batch b and leaves its supported points compacted in buffer `buf`; returns their count
+    auto load_batch = [&](int b, int buf) -> int {
+        const int n = first + b * kWarps * 32 + lane;
         int cell = -1;
         if (n < N) cell = project_and_flag(c, R, t, n);
-        unsigned mask = __ballot_sync(0xffffffffu, cell >= 0);
-        while (mask) {
-            const unsigned j = __fns(mask, 0, sg + 1);  // the sg-th supported point still to do
-            const bool act = j != 0xffffffffu;
-            const int cj = __shfl_sync(0xffffffffu, cell, act ? (int)j : 0);
-            const int nj = base + (int)j;
-            double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-            if (act) {
-                const float4* pF = reinterpret_cast<const float4*>(q.F + (size_t)cj * q.C + c.c0);
-                const float4* pR = reinterpret_cast<const float4*>(q.ref + (size_t)nj * q.C + c.c0);
-                const float4* pGx = GRAD ? reinterpret_cast<const float4*>(q.Gx + (size_t)cj * q.C + c.c0) : nullptr;
-                const float4* pGy = GRAD ? reinterpret_cast<const float4*>(q.Gy + (size_t)cj * q.C + c.c0) : nullptr;
-                for (int v0 = sl; v0 < nvec; v0 += L * KB) {
-                    float4 f[KB], r[KB], gx[KB], gy[KB];
+        const unsigned mask = __ballot_sync(0xffffffffu, cell >= 0);
+        if (cell >= 0) {
+            const int rank = __popc(mask & ((1u << lane) - 1u));
+            sh.bl_cell[warp][buf][rank] = cell;
+            sh.bl_n[warp][buf][rank] = n;
+        }
+        __syncwarp();
+        return __popc(mask);
+    };
+    auto items_of = [&](int cnt) -> int { return SHORT ? (cnt + G - 1) >> (5 - LOG2L) : cnt * nCh; };
+
+    // copies `nv` float4 of the ROWS rows of point k (buffer buf), starting at channel offset `off`
+    // bytes, to shared address dst (rows packed back to back)
+    auto copy_point = [&](int buf, int k, uint32_t off, int nv, uint32_t dst) {
+        const uint32_t cell = (uint32_t)bcell[buf * 32 + k], n = (uint32_t)bn[buf * 32 + k];
+        const char* s[4];
+        s[0] = baseF + (size_t)cell * pitch + off;
+        s[ROWS - 1] = baseR + (size_t)n * pitch + off;
+        if (GRAD) {
+            s[1] = baseGx + (size_t)cell * pitch + off;
+            s[2] = baseGy + (size_t)cell * pitch + off;
+        }
+        dst += lane * 16;
 #pragma unroll
-                    for (int k = 0; k < KB; ++k) {
-                        const int v = v0 + k * L;
-                        const bool in = v < nvec;
-                        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-                        f[k] = in ? ldg_stream(pF + v) : z;
-                        r[k] = in ? ldg_stream(pR + v) : z;
-                        gx[k] = (GRAD && in) ? ldg_stream(pGx + v) : z;
-                        gy[k] = (GRAD && in) ? ldg_stream(pGy + v) : z;
-                    }
+        for (int r = 0; r < ROWS; ++r) {
+            const uint32_t d = dst + (uint32_t)(r * nv) * 16u;
+            if (SHORT) {  // nv <= 64
+                if (lane < nv) cp_async16_s(d, s[r]);
+                if (lane + 32 < nv) cp_async16_s(d + 512, s[r] + 512);
+            } else {
+                for (int v = lane; v < nv; v += 32) cp_async16_s(d + (uint32_t)(v - lane) * 16u, s[r] + (size_t)(v - lane) * 16);
+            }
+        }
+    };
+
+    int ik = 0, ich = 0;  // issue side: point / chunk of the next item (long rows)
+    auto issue = [&](int buf, int cnt, int it, int slot) {
+        const uint32_t dst0 = ring + (uint32_t)slot * slot_bytes;
+        if (SHORT) {
+            const int k0 = it * G, gc = min(G, cnt - k0);
+            for (int g = 0; g < gc; ++g) copy_point(buf, k0 + g, 0u, Cl >> 2, dst0 + (uint32_t)(g * ROWS * Cl) * 4u);
+        } else {
+            const int off = ich * CH;
+            copy_point(buf, ik, (uint32_t)off * 4u, min(CH, Cl - off) >> 2, dst0);
+            if (++ich == nCh) {
+                ich = 0;
+                ++ik;
+            }
+        }
+        cp_async_commit();
+    };
+
+    double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    int ck = 0, cch = 0;  // consume side: point / chunk of the next item (long rows)
+    auto consume = [&](int buf, int cnt, int it, int slot, int inflight) {
+        cp_async_wait_pending(inflight - 1);  // the oldest of the `inflight` groups has landed
+        __syncwarp();
+        const uint32_t src0 = ring + (uint32_t)slot * slot_bytes;
+        if (SHORT) {
+            const int sg = lane >> LOG2L, sl = lane & (L - 1);
+            const int k = it * G + sg, nvec = Cl >> 2;
+            const bool act = k < cnt;
 #pragma unroll
-                    for (int k = 0; k < KB; ++k) {
-                        acc1<GRAD>(f[k].x, r[k].x, gx[k].x, gy[k].x, a);
-                        acc1<GRAD>(f[k].y, r[k].y, gx[k].y, gy[k].y, a);
-                        acc1<GRAD>(f[k].z, r[k].z, gx[k].z, gy[k].z, a);
-                        acc1<GRAD>(f[k].w, r[k].w, gx[k].w, gy[k].w, a);
-                    }
-                }
+            for (int i = 0; i < 6; ++i) a[i] = 0.0;
+            const uint32_t rowB = (uint32_t)Cl * 4u;
+            const uint32_t p = src0 + (uint32_t)sg * ROWS * rowB + (uint32_t)sl * 16u;
+            if (act && sl < nvec) acc4<GRAD>(p, p + rowB, p + 2 * rowB, p + (ROWS - 1) * rowB, a);
+            if (act && sl + L < nvec) {
+                const uint32_t p2 = p + L * 16;
+                acc4<GRAD>(p2, p2 + rowB, p2 + 2 * rowB, p2 + (ROWS - 1) * rowB, a);
             }
-            constexpr int NV = GRAD ? 6 : 1;
-            for (int off = L >> 1; off > 0; off >>= 1) {
+            reduce_lanes<GRAD, LOG2L>(a);
+            if (act && sl == 0) write_record<GRAD>(a, c.rec + (size_t)bn[buf * 32 + k] * kRecDoubles);
+        } else {
+            if (cch == 0) {
 #pragma unroll
-                for (int i = 0; i < NV; ++i) a[i] = __dadd_rn(a[i], shfl_xor_f64(a[i], off));
+                for (int i = 0; i < 6; ++i) a[i] = 0.0;
             }
-            if (act && sl == 0) {
-                double2* o = reinterpret_cast<double2*>(c.rec + (size_t)nj * kRecDoubles);
-                o[0] = make_double2(a[0], a[1]);
-                if (GRAD) {
-                    o[1] = make_double2(a[2], a[3]);
-                    o[2] = make_double2(a[4], a[5]);
-                }
+            const int nv = min(CH, Cl - cch * CH) >> 2;
+            const uint32_t rowB = (uint32_t)nv * 16u;
+            uint32_t p = src0 + (uint32_t)lane * 16u;
+#pragma unroll 2
+            for (int v = lane; v < nv; v += 32, p += 512) acc4<GRAD>(p, p + rowB, p + 2 * rowB, p + (ROWS - 1) * rowB, a);
+            if (++cch == nCh) {
+                cch = 0;
+                reduce_lanes<GRAD, 5>(a);
+                if (lane == 0) write_record<GRAD>(a, c.rec + (size_t)bn[buf * 32 + ck] * kRecDoubles);
+                ++ck;
             }
-            for (int g = 0; g < G && mask; ++g) mask &= mask - 1;  // drop the G points just done
+        }
+        __syncwarp();  // every lane is done with the slot: it may be refilled
+    };
+
+    int cnt0 = load_batch(0, 0), cnt1 = 0;
+    int ib = 0, ii = 0, cb = 0, ci = 0, inflight = 0;
+    int items_i = items_of(cnt0), items_c = items_i;
+    for (;;) {
+        // ---- issue side: keep `depth` items in flight, at most one batch ahead of the consume side
+        for (;;) {
+            if (ii < items_i) {
+                if (inflight == depth) break;
+                int slot = rp.pos + inflight;
+                if (slot >= depth) slot -= depth;
+                issue(ib & 1, (ib & 1) ? cnt1 : cnt0, ii, slot);
+                ++ii;
+                ++inflight;
+            } else {
+                if (ib + 1 >= nb || ib > cb) break;
+                ++ib;
+                ii = 0;
+                ik = 0;
+                ich = 0;
+                const int cnew = load_batch(ib, ib & 1);
+                if (ib & 1)
+                    cnt1 = cnew;
+                else
+                    cnt0 = cnew;
+                items_i = items_of(cnew);
+            }
+        }
+        // ---- consume side
+        if (ci < items_c) {
+            consume(cb & 1, (cb & 1) ? cnt1 : cnt0, ci, rp.pos, inflight);
+            if (++rp.pos == depth) rp.pos = 0;
+            ++ci;
+            --inflight;
+        } else {
+            if (cb == ib) break;  // the issue side could not advance: that was the last batch
+            ++cb;
+            ci = 0;
+            ck = 0;
+            cch = 0;
+            items_c = items_of((cb & 1) ? cnt1 : cnt0);
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// Streaming phase: one record per supported point.
+// Streaming phase: one record per supported point.  Every warp is its own producer and consumer.
 // ---------------------------------------------------------------------------------------------
 template <bool GRAD>
 __device__ void stream_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const QueryDev& q = *c.q;
-    constexpr int ROWS = GRAD ? 4 : 2;
     const int N = c.n1;
 
-    if (c.aligned) {
-        const int CH = c.CH, nCh = c.nCh;
-        if (warp == 0) {
-            // ---------------- producer: float64 projection + TMA issue.
-            // Four lanes serve each consumer warp ("feeder" fw): lane fr issues the bulk copy of row
-            // fr.  The feeders poll their slot's `empty` barrier with the non-blocking test_wait in a
-            // warp-convergent loop -- no lane ever blocks, so one slow consumer never stalls the
-            // other seven sub-rings and the warp does not serialise on divergent spin loops.
-            constexpr int LPF = 32 / kConsumerWarps;  // lanes per feeder == points per feeder per batch
-            static_assert(LPF >= 4, "need one lane per staged row");
-            const int fw = lane / LPF, fr = lane % LPF;
-            for (int base = c.n0; base < N; base += 32) {
-                const int n = base + lane;
-                int cell = -1;
-                if (n < N) cell = project_and_flag(c, R, t, n);
-                sh.cellbuf[lane] = cell;
-                __syncwarp();
-                int jj = 0, ch = 0;
-                for (;;) {
-                    while (jj < LPF && sh.cellbuf[fw + kConsumerWarps * jj] < 0) ++jj;  // next supported point
-                    const bool have = jj < LPF;
-                    if (!__any_sync(0xffffffffu, have)) break;
-                    const int slot = fw * c.depth + rp.pos;    // staging memory
-                    const int bar = fw * kMaxDepth + rp.pos;   // its barriers / meta
-                    const bool go = have && mbar_test(&sh.empty[bar], rp.phase() ^ 1u);
-                    const int j = fw + kConsumerWarps * (have ? jj : 0);
-                    const int cj = sh.cellbuf[j], nj = base + j;
-                    const int off = ch * CH;
-                    const uint32_t rowB = (uint32_t)min(CH, c.Cl - off) * 4u;
-                    if (go && fr == 0) {
-                        sh.meta[bar] = make_int2(nj, ch | ((ch == nCh - 1) ? (1 << 30) : 0));
-                        mbar_arrive_expect_tx(&sh.full[bar], (uint32_t)ROWS * rowB);
-                    }
-                    __syncwarp();
-                    if (go && fr < ROWS) {
-                        const float* src;
-                        if (fr == ROWS - 1)
-                            src = q.ref + (size_t)nj * q.C;
-                        else
-                            src = (fr == 0 ? q.F : (fr == 1 ? q.Gx : q.Gy)) + (size_t)cj * q.C;
-                        tma_bulk_g2s(c.ring + (size_t)slot * c.slot_bytes + fr * rowB, src + c.c0 + off, rowB,
-                                     &sh.full[bar]);
-                    }
-                    if (go) {
-                        rp.advance(c.depth);
-                        if (++ch == nCh) {
-                            ch = 0;
-                            ++jj;
-                        }
-                    }
-                    if (!__any_sync(0xffffffffu, go)) __nanosleep(40);
-                }
-                __syncwarp();
-            }
-            {  // end-of-evaluation sentinel for every consumer warp
-                bool posted = false;
-                for (;;) {
-                    if (!posted) {
-                        const int bar = fw * kMaxDepth + rp.pos;
-                        if (mbar_test(&sh.empty[bar], rp.phase() ^ 1u)) {
-                            if (fr == 0) {
-                                sh.meta[bar] = make_int2(-1, 0);
-                                mbar_arrive(&sh.full[bar]);
-                            }
-                            rp.advance(c.depth);
-                            posted = true;
-                        }
-                    }
-                    if (__all_sync(0xffffffffu, posted)) break;
-                    __nanosleep(40);
-                }
-            }
-        } else {
-            // ---------------- consumers: warp w drains sub-ring w
-            const int w = warp - 1;
-            double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-            for (;;) {
-                const int slot = w * c.depth + rp.pos, bar = w * kMaxDepth + rp.pos;
-                mbar_wait(&sh.full[bar], rp.phase());
-                const int2 m = sh.meta[bar];
-                rp.advance(c.depth);
-                if (m.x < 0) {
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&sh.empty[bar]);
-                    break;
-                }
-                const int ch = m.y & 0xffff;
-                if (ch == 0) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) a[i] = 0.0;
-                }
-                const int cnt = min(CH, c.Cl - ch * CH);
-                accum_slot<GRAD>(c.ring + (size_t)slot * c.slot_bytes, cnt >> 2, lane, a);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[bar]);  // slot may be refilled
-                if (m.y >> 30) finish_point<GRAD>(a, lane, c.rec + (size_t)m.x * kRecDoubles);
-            }
-        }
-    } else {
+    if (!c.aligned) {
         // ---------------- generic path: every warp projects its own 32 points, loads directly
         for (int base = c.n0 + warp * 32; base < N; base += kWarps * 32) {
             const int n = base + lane;
@@ -412,9 +399,18 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
                     }
                     acc1<GRAD>(f, r, gx, gy, a);
                 }
-                finish_point<GRAD>(a, lane, c.rec + (size_t)nj * kRecDoubles);
+                reduce_lanes<GRAD, 5>(a);
+                if (lane == 0) write_record<GRAD>(a, c.rec + (size_t)nj * kRecDoubles);
             }
         }
+        return;
+    }
+
+    switch (c.L) {
+        case 4: stream_staged<GRAD, 2>(c, R, t, sh, rp); break;
+        case 8: stream_staged<GRAD, 3>(c, R, t, sh, rp); break;
+        case 16: stream_staged<GRAD, 4>(c, R, t, sh, rp); break;
+        default: stream_staged<GRAD, 5>(c, R, t, sh, rp); break;
     }
 }
 
@@ -559,17 +555,12 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     const double limit = use_ratio ? sh.limit : 0.0;
 
     const double fx = q.K[0], fy = q.K[4];
-    int per = c.range_len;                     // points per fixed range
-    int r_first = c.crank * (kRanges / c.csize);
-    int r_count = kRanges / c.csize;
-    if (c.experiment & 1) r_count = 1;  // TEMPORARY experiment: one range per CTA (non-canonical order)
+    const int per = c.range_len;  // points per fixed range
+    const int r_first = c.crank * (kRanges / c.csize);
+    const int r_count = kRanges / c.csize;
     int32_t tot_i = 0;  // warp 0, lanes 0 / 1: survivors / supported of this CTA
     for (int rr = 0; rr < r_count; ++rr) {
-        int r0 = min(q.N, (r_first + rr) * per), r1 = min(q.N, r0 + per);
-        if (c.experiment & 1) {
-            r0 = c.n0;
-            r1 = c.n1;
-        }
+        const int r0 = min(q.N, (r_first + rr) * per), r1 = min(q.N, r0 + per);
         double acc[28];
 #pragma unroll
         for (int i = 0; i < 28; ++i) acc[i] = 0.0;
@@ -637,7 +628,6 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     else
         __syncthreads();
     if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;  // mean; 0/0 = NaN like torch's empty mean
-    fence_proxy_async();  // the ring was used as scratch through the generic proxy; TMA writes it next
     __syncthreads();
 }
 
@@ -645,10 +635,7 @@ template <bool GRAD>
 __device__ __forceinline__ void evaluate(EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     set_geometry(c, GRAD ? 4 : 2);
     rp.pos = 0;  // the ring is empty between evaluations; its depth may change with the slice
-    if (c.aligned && c.Cl <= c.direct_max_c)
-        stream_points_direct<GRAD, 4>(c, R, t);
-    else
-        stream_points<GRAD>(c, R, t, sh, rp);
+    stream_points<GRAD>(c, R, t, sh, rp);
     __syncthreads();
     reduce_points<GRAD>(c, R, t, sh, rp);
     if (threadIdx.x == 0) {
@@ -739,12 +726,6 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     // combined through distributed shared memory, and every CTA then takes the same LM decisions.
     const int csize = p.cluster_size, crank = csize > 1 ? (int)cg::this_cluster().block_rank() : 0;
     if (csize > 1) cg::this_cluster().sync();  // every CTA of the cluster is resident before any remote access
-    if (tid < kConsumerWarps * kMaxDepth) {
-        mbar_init(&sh.full[tid], 1);
-        mbar_init(&sh.empty[tid], 1);
-        mbar_fence_init();
-    }
-    __syncthreads();
     RingPos rp;
     rp.pos = 0;
     rp.bits = 0;
@@ -778,8 +759,6 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.min_depth = p.min_depth;
         c.csize = csize;
         c.crank = crank;
-        c.experiment = p.experiment;
-        c.direct_max_c = p.direct_max_c;
         {
             const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
             c.range_len = per;

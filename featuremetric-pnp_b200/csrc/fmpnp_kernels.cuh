@@ -8,9 +8,8 @@
 
 namespace fmpnp {
 
-constexpr int kConsumerWarps = 8;                 // one sub-ring of the shared-memory staging ring each
-constexpr int kWarps = kConsumerWarps + 1;        // + 1 producer warp (projection + TMA issue)
-constexpr int kThreads = kWarps * 32;             // 288
+constexpr int kWarps = 8;                         // each streams its own points through its slice of the ring
+constexpr int kThreads = kWarps * 32;             // 256
 constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
 constexpr int kRanges = 16;                       // fixed reduction ranges per query == max cluster size
 constexpr int kMaxDepth = 8;                      // max slots per sub-ring
@@ -61,11 +60,9 @@ struct LaunchParams {
     int32_t n_max;
     unsigned int* work_counter;
     // staging ring geometry (slot size / depth are derived per evaluation, see set_geometry)
-    int32_t ring_per_warp;  // bytes of the shared-memory ring owned by one consumer warp
-    int32_t min_depth;      // minimum slots per consumer warp
+    int32_t ring_per_warp;  // bytes of the shared-memory ring owned by one warp
+    int32_t min_depth;      // minimum slots per warp
     int32_t cluster_size;   // CTAs per query (thread-block cluster); grid = clusters * cluster_size
-    int32_t experiment;
-    int32_t direct_max_c;   // channel slices up to this length are streamed without shared-memory staging
 };
 
 // Host-side launchers (defined in fmpnp_kernels.cu)
