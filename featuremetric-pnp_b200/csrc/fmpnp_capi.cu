@@ -432,4 +432,52 @@ int fmpnp_pack_chw_to_hwc(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, f
     return FMPNP_SUCCESS;
 }
 
+int fmpnp_sobel_pack(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, float* F, float* Gx, float* Gy, int32_t C,
+                     int32_t Hf, int32_t Wf, int32_t border, int32_t normalized, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!src || !F || !Gx || !Gy || C < 1 || Hf < 1 || Wf < 1 ||
+        (border != FMPNP_BORDER_REPLICATE && border != FMPNP_BORDER_ZERO))
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad sobel_pack arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, launch_sobel_pack(src, src_is_f64, F, Gx, Gy, C, Hf, Wf, border == FMPNP_BORDER_ZERO, normalized,
+                                      static_cast<cudaStream_t>(stream_)));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_gather_descriptors(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, const int32_t* rows, const int32_t* cols,
+                             float* dst, int32_t C, int32_t H, int32_t W, int32_t N, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (N == 0) return FMPNP_SUCCESS;
+    if (!src || !rows || !cols || !dst || C < 1 || H < 1 || W < 1 || N < 0)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad gather_descriptors arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, launch_gather_chw_rows(src, src_is_f64, rows, cols, dst, C, H, W, N, static_cast<cudaStream_t>(stream_)));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_resize_bilinear_chw(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, double* dst, int32_t C, int32_t H,
+                              int32_t W, int32_t Ho, int32_t Wo, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!src || !dst || C < 1 || H < 1 || W < 1 || Ho < 1 || Wo < 1)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad resize arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, launch_bilinear_resize_chw(src, src_is_f64, dst, C, H, W, Ho, Wo, static_cast<cudaStream_t>(stream_)));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_blur_chw(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, const double* kernel, double* dst, int32_t C,
+                   int32_t H, int32_t W, int32_t k, int32_t pad, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!src || !kernel || !dst || C < 1 || H < 1 || W < 1 || k < 1 || pad < 0 || H + 2 * pad - k + 1 < 1 ||
+        W + 2 * pad - k + 1 < 1)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad blur arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, launch_blur_chw(src, src_is_f64, kernel, dst, C, H, W, k, pad, static_cast<cudaStream_t>(stream_)));
+    ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
 }  // extern "C"

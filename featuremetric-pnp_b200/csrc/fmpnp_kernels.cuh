@@ -69,6 +69,14 @@ struct LaunchParams {
 cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaStream_t stream);
 cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, int C, int Hf, int Wf,
                                    cudaStream_t stream);
+cudaError_t launch_sobel_pack(const void* src, int src_is_f64, float* F, float* Gx, float* Gy, int C, int H, int W,
+                              int zero_pad, int normalized, cudaStream_t stream);
+cudaError_t launch_gather_chw_rows(const void* src, int src_is_f64, const int32_t* rows, const int32_t* cols, float* dst,
+                                   int C, int H, int W, int N, cudaStream_t stream);
+cudaError_t launch_bilinear_resize_chw(const void* src, int src_is_f64, double* dst, int Cs, int H, int W, int Ho, int Wo,
+                                       cudaStream_t stream);
+cudaError_t launch_blur_chw(const void* src, int src_is_f64, const double* kern, double* dst, int Cs, int H, int W, int k,
+                            int pad, cudaStream_t stream);
 size_t refine_static_smem_bytes();
 int max_active_clusters(int cluster_size, int ring_bytes);
 cudaError_t refine_allow_nonportable_clusters(int allow);

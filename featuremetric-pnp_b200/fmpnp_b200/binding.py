@@ -93,6 +93,18 @@ def lib():
             L.fmpnp_pack_chw_to_hwc.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
                                                 C.c_int32, C.c_void_p]
             L.fmpnp_pack_chw_to_hwc.restype = C.c_int
+            L.fmpnp_sobel_pack.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+            L.fmpnp_sobel_pack.restype = C.c_int
+            L.fmpnp_gather_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+            L.fmpnp_gather_descriptors.restype = C.c_int
+            L.fmpnp_resize_bilinear_chw.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+                                                    C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+            L.fmpnp_resize_bilinear_chw.restype = C.c_int
+            L.fmpnp_blur_chw.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                         C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+            L.fmpnp_blur_chw.restype = C.c_int
             _lib = L
     return _lib
 
@@ -344,4 +356,73 @@ def pack_chw_to_hwc(src, ctx=None):
     rc = lib().fmpnp_pack_chw_to_hwc(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
                                      C.c_void_p(dst.data_ptr()), Cn, Hf, Wf, _stream_ptr())
     ctx.check(rc, "fmpnp_pack_chw_to_hwc")
+    return dst
+
+
+def _check_chw(src, what):
+    if not (isinstance(src, torch.Tensor) and src.is_cuda and src.dim() == 3 and src.is_contiguous()
+            and src.dtype in (torch.float32, torch.float64)):
+        raise FmpnpError("%s expects a contiguous CUDA float32/float64 (C, H, W) tensor" % what)
+    return (int(v) for v in src.shape)
+
+
+def sobel_pack(src, border="replicate", normalized=False, ctx=None):
+    """CHW map -> (F, Gx, Gy) HWC float32: the reference's sobel_filter fused with the layout pack."""
+    ctx = ctx or default_context()
+    Cn, Hf, Wf = _check_chw(src, "sobel_pack")
+    outs = [torch.empty((Hf, Wf, Cn), dtype=torch.float32, device=src.device) for _ in range(3)]
+    rc = lib().fmpnp_sobel_pack(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
+                                C.c_void_p(outs[0].data_ptr()), C.c_void_p(outs[1].data_ptr()),
+                                C.c_void_p(outs[2].data_ptr()), Cn, Hf, Wf, {"replicate": 0, "zero": 1}[border],
+                                1 if normalized else 0, _stream_ptr())
+    ctx.check(rc, "fmpnp_sobel_pack")
+    return tuple(outs)
+
+
+def gather_descriptors(src, rows, cols, ctx=None):
+    """feature_ref[n] = src[:, rows[n], cols[n]] as an (N, C) float32 CUDA tensor."""
+    ctx = ctx or default_context()
+    Cn, H, W = _check_chw(src, "gather_descriptors")
+    rows = torch.as_tensor(rows).to(device=src.device, dtype=torch.int32).contiguous()
+    cols = torch.as_tensor(cols).to(device=src.device, dtype=torch.int32).contiguous()
+    N = int(rows.numel())
+    if int(cols.numel()) != N:
+        raise FmpnpError("rows / cols length mismatch")
+    if N and (int(rows.min()) < -H or int(rows.max()) >= H or int(cols.min()) < -W or int(cols.max()) >= W):
+        raise IndexError("descriptor cell outside the %d x %d reference map" % (H, W))
+    dst = torch.empty((N, Cn), dtype=torch.float32, device=src.device)
+    rc = lib().fmpnp_gather_descriptors(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
+                                        C.c_void_p(rows.data_ptr()), C.c_void_p(cols.data_ptr()),
+                                        C.c_void_p(dst.data_ptr()), Cn, H, W, N, _stream_ptr())
+    ctx.check(rc, "fmpnp_gather_descriptors")
+    return dst
+
+
+def resize_bilinear_chw(src, Ho, Wo, ctx=None):
+    """nn.functional.interpolate(src[None], size=(Ho, Wo), mode='bilinear')[0] in float64."""
+    ctx = ctx or default_context()
+    Cn, H, W = _check_chw(src, "resize_bilinear_chw")
+    dst = torch.empty((Cn, int(Ho), int(Wo)), dtype=torch.float64, device=src.device)
+    rc = lib().fmpnp_resize_bilinear_chw(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
+                                         C.c_void_p(dst.data_ptr()), Cn, H, W, int(Ho), int(Wo), _stream_ptr())
+    ctx.check(rc, "fmpnp_resize_bilinear_chw")
+    return dst
+
+
+def blur_chw(src, kernel, pad=1, ctx=None):
+    """Depthwise conv2d of a CHW map with one k x k kernel and zero padding `pad`, in float64."""
+    ctx = ctx or default_context()
+    Cn, H, W = _check_chw(src, "blur_chw")
+    kern = torch.as_tensor(kernel).to(device=src.device, dtype=torch.float64).contiguous()
+    k = int(kern.shape[0])
+    if kern.dim() != 2 or int(kern.shape[1]) != k:
+        raise FmpnpError("blur kernel must be k x k")
+    Ho, Wo = H + 2 * pad - k + 1, W + 2 * pad - k + 1
+    if Ho < 1 or Wo < 1:
+        raise FmpnpError("blur kernel larger than the padded map")
+    dst = torch.empty((Cn, Ho, Wo), dtype=torch.float64, device=src.device)
+    rc = lib().fmpnp_blur_chw(ctx._h, C.c_void_p(src.data_ptr()), 1 if src.dtype == torch.float64 else 0,
+                              C.c_void_p(kern.data_ptr()), C.c_void_p(dst.data_ptr()), Cn, H, W, k, int(pad),
+                              _stream_ptr())
+    ctx.check(rc, "fmpnp_blur_chw")
     return dst

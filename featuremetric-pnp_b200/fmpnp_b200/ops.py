@@ -6,7 +6,7 @@ the `fmpnp_problem` descriptors and calls libfmpnp.so on the current CUDA stream
 registered for the CUDA backend alone -- calling them with CPU tensors raises, there is no CPU
 kernel behind them.
 
-    out = torch.ops.fmpnp.refine_batch(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, opts_f64, levels, track)
+    out = torch.ops.fmpnp.refine_batch(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, opts_f64, levels, track, active)
       F, Gx, Gy : lists of (Hf, Wf, C) float32 CUDA tensors (one per query)
       ref       : list of (N, C) float32;  pts3D: list of (N, 3) float64
       K, R0, t0 : (B, 3, 3), (B, 3, 3), (B, 3) float64 CPU tensors
@@ -14,6 +14,7 @@ kernel behind them.
       opts_f64  : (6,) float64 CPU tensor [n_iters, loss_id, barron_alpha, lambda_, ratio_threshold (nan = None), solver]
       levels    : (L, 2) int32 CPU tensor of channel slices (L = 0: plain forward)
       track     : bool; True also returns the per-iteration history (the reference's track_)
+      active    : [] or one (N,) uint8 CUDA mask per query: points with 0 are left out (== pts3D[inliers])
       returns   : [results] or [results, len, Rs, ts, costs, points2d, mask, kept]; results is a
                   (B, 168) uint8 CUDA tensor of fmpnp_result records (view with binding.RESULT_DTYPE)
 """
@@ -26,17 +27,18 @@ from . import binding as _b
 _LOSS_NAMES = {v: k for k, v in _b.LOSS_IDS.items()}
 
 
-def _problems(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, grads=True):
+def _problems(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, grads=True, active=None):
     B = len(F)
     return [_b.Problem(F[i], Gx[i] if grads else None, Gy[i] if grads else None, ref[i], pts3D[i], K[i], R0[i], t0[i],
-                       int(im_size[i, 0]), int(im_size[i, 1])) for i in range(B)]
+                       int(im_size[i, 0]), int(im_size[i, 1]), active=active[i] if active else None) for i in range(B)]
 
 
 @torch.library.custom_op("fmpnp::refine_batch", mutates_args=(), device_types="cuda")
 def refine_batch(F: List[torch.Tensor], Gx: List[torch.Tensor], Gy: List[torch.Tensor], ref: List[torch.Tensor],
                  pts3D: List[torch.Tensor], K: torch.Tensor, R0: torch.Tensor, t0: torch.Tensor, im_size: torch.Tensor,
-                 opts_f64: torch.Tensor, levels: torch.Tensor, track: bool) -> List[torch.Tensor]:
-    probs = _problems(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size)
+                 opts_f64: torch.Tensor, levels: torch.Tensor, track: bool,
+                 active: List[torch.Tensor]) -> List[torch.Tensor]:
+    probs = _problems(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, active=active)
     o = [float(v) for v in opts_f64.tolist()]
     rt = None if o[4] != o[4] else o[4]
     lv = [(int(a), int(b)) for a, b in levels.tolist()] if levels.numel() else None
@@ -55,7 +57,7 @@ HISTORY_KEYS = ("len", "Rs", "ts", "costs", "points2d", "mask", "kept")
 
 
 @refine_batch.register_fake
-def _(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, opts_f64, levels, track):
+def _(F, Gx, Gy, ref, pts3D, K, R0, t0, im_size, opts_f64, levels, track, active):
     B, dev = len(F), F[0].device
     res = [torch.empty((B, _b.RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)]
     if track:

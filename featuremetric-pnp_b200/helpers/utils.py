@@ -88,6 +88,16 @@ def sobel_filter(feature_map, batch=False, normalized=False):
     return gx.reshape(feature_map.shape), gy.reshape(feature_map.shape)
 
 
+def gaussian_kernel2d(kernel_size, sigma):
+    """k x k Gaussian window as kornia 0.2.2's get_gaussian_kernel2d((k, k), (sigma, sigma)) builds it
+    (float32: exp(-(x - k // 2)^2 / (2 sigma^2)) normalised to sum 1, outer product), returned in float64
+    as the reference casts it (model.py:199-200).  kornia is not vendored by the reference: parity unpinned."""
+    x = torch.arange(int(kernel_size), dtype=torch.float32) - int(kernel_size) // 2
+    g = torch.exp(-(x * x) / float(2 * sigma ** 2))
+    g = g / g.sum()
+    return torch.outer(g, g).double()
+
+
 def to_homogeneous(points):
     if isinstance(points, torch.Tensor):
         return torch.cat([points, points.new_ones(points.shape[:-1] + (1,))], dim=-1)

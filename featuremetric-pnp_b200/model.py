@@ -31,8 +31,8 @@ except ImportError:  # pragma: no cover
     from helpers import _gin_shim as gin
 
 import fmpnp_b200 as _fm
-from helpers.utils import (barron_loss, cauchy_loss, geman_mcclure_loss, huber_loss, scaled_loss,  # noqa: F401
-                           sobel_filter, squared_loss)
+from helpers.utils import (barron_loss, cauchy_loss, gaussian_kernel2d, geman_mcclure_loss, huber_loss,  # noqa: F401
+                           scaled_loss, sobel_filter, squared_loss)
 
 # ------------------------------------------------------------------------------------------------
 # packing cache: CHW (reference layout) -> HWC fp32 on the device, keyed by the source tensor
@@ -129,8 +129,10 @@ class sparseFeaturePnP(nn.Module):
         self.track_["threshold_mask"].append(threshold_mask)
 
     # -- shared tail of forward / multilevel_optimization ---------------------------------------
-    def _run(self, prob, levels, track):
-        """One query through torch.ops.fmpnp.refine_batch (PyTorch custom op -> C ABI -> CUDA kernel)."""
+    def _run(self, prob, levels, track, select=None):
+        """One query through torch.ops.fmpnp.refine_batch (PyTorch custom op -> C ABI -> CUDA kernel).
+        `select`: boolean mask over the points; the history is reported for those points only (a
+        caller that passes pts3D[inliers] to the reference sees exactly these rows)."""
         loss_id, alpha = _fm.loss_id_of(self.loss_fn)
         rt = float("nan") if self.ratio_threshold_ is None else float(self.ratio_threshold_)
         solver = {"cholesky": 0, "lu": 1}[self.solver]
@@ -140,19 +142,21 @@ class sparseFeaturePnP(nn.Module):
         outs = torch.ops.fmpnp.refine_batch(
             [prob.F], [prob.Gx], [prob.Gy], [prob.ref], [prob.pts3D], torch.from_numpy(prob.K.reshape(1, 3, 3)),
             torch.from_numpy(prob.R0.reshape(1, 3, 3)), torch.from_numpy(prob.t0.reshape(1, 3)),
-            torch.tensor([[prob.im_width, prob.im_height]], dtype=torch.int32), opts, lv, bool(track))
+            torch.tensor([[prob.im_width, prob.im_height]], dtype=torch.int32), opts, lv, bool(track),
+            [prob.active] if prob.active is not None else [])
         r = outs[0].cpu().numpy().view(_fm.binding.RESULT_DTYPE).reshape(-1)[0]
         if track:
             h = {k: v.cpu().numpy() for k, v in zip(_fm.ops.HISTORY_KEYS, outs[1:])}
             n = int(h["len"][0])
             N = prob.N
+            sel = slice(None) if select is None else np.asarray(select, dtype=bool)
             for e in range(n):
-                m = torch.from_numpy(h["mask"][0, e, :N].astype(bool))
+                m = torch.from_numpy(h["mask"][0, e, :N].astype(bool)[sel])
                 thr = None
                 if self.use_ratio_test_:
-                    thr = torch.from_numpy(h["kept"][0, e, :N].astype(bool))[m]
+                    thr = torch.from_numpy(h["kept"][0, e, :N].astype(bool)[sel])[m]
                 self.track(torch.from_numpy(h["Rs"][0, e].copy()), torch.from_numpy(h["ts"][0, e].copy()),
-                           float(h["costs"][0, e]), torch.from_numpy(h["points2d"][0, e, :N].copy()), m, thr)
+                           float(h["costs"][0, e]), torch.from_numpy(h["points2d"][0, e, :N][sel].copy()), m, thr)
             if self.verbose:
                 for e in range(n):
                     print("entry", e, float(h["costs"][0, e]))
@@ -179,21 +183,67 @@ class sparseFeaturePnP(nn.Module):
                 return R_init, t_init
             return self.forward(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width,
                                 im_height, R_init=R_init, t_init=t_init, track=track)
-        levels = []
-        for start, end, target_size, kernel_size in feature_pyramid:
-            if target_size is not None or kernel_size is not None:
-                raise NotImplementedError(
-                    "pyramid levels with target_size / kernel_size (resize / blur, reference model.py:196-207) are "
-                    "not built yet: no shipped config uses them and their kornia 0.2.2 kernels cannot be pinned")
-            levels.append((int(start), int(end)))
+        if any(ts is not None or ks is not None for _, _, ts, ks in feature_pyramid):
+            return self._multilevel_resampled(feature_pyramid, pts3D, feature_ref, feature_map_query, feature_grad_x,
+                                              feature_grad_y, K, im_width, im_height, R_init, t_init, track)
+        levels = [(int(start), int(end)) for start, end, _, _ in feature_pyramid]
         prob = _problem(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height,
                         R_init, t_init)
-        R, t, r = self._run(prob, levels, track)
+        return self.multilevel_packed(levels, prob, track=track)
+
+    def _multilevel_resampled(self, feature_pyramid, pts3D, feature_ref, feature_map_query, feature_grad_x,
+                              feature_grad_y, K, im_width, im_height, R_init, t_init, track):
+        """Pyramid with per-level resize (`target_size`) and / or Gaussian blur (`kernel_size`), reference
+        model.py:193-210.  Each such level gets its own maps: channel slice -> bilinear resize -> depthwise
+        blur (sigma = 1, zero padding 1 whatever the kernel size, as the reference) -> Sobel, all by the CUDA
+        kernels of libfmpnp (float64 arithmetic, float32 storage); then one forward() per level."""
+        self.initial_cost_ = self.compute_cost(pts3D, R_init, t_init, feature_map_query, feature_ref, K, im_width,
+                                               im_height)
+        if self.initial_cost_ is None:
+            return R_init, t_init
+        dev = _device()
+        src = feature_map_query
+        if src.dtype not in (torch.float32, torch.float64):
+            src = src.double()
+        src = src.to(dev).contiguous()
+        ref = _dev_tensor(feature_ref, torch.float32)
+        pts = _dev_tensor(pts3D, torch.float64).reshape(-1, 3)
+        R, t = R_init, t_init
+        for start, end, target_size, kernel_size in feature_pyramid:
+            start, end = int(start), int(end)
+            ref_l = ref[:, start:end].contiguous()
+            if target_size is None and kernel_size is None:
+                F = _pack_map(feature_map_query)[:, :, start:end].contiguous()
+                Gx = _pack_map(feature_grad_x)[:, :, start:end].contiguous()
+                Gy = _pack_map(feature_grad_y)[:, :, start:end].contiguous()
+            else:
+                local = src[start:end]
+                if target_size is not None:
+                    local = _fm.resize_bilinear_chw(local, int(target_size), int(target_size))
+                if kernel_size is not None:
+                    local = _fm.blur_chw(local, gaussian_kernel2d(int(kernel_size), 1.0), pad=1)
+                F, Gx, Gy = _fm.sobel_pack(local)
+            prob = _fm.Problem(F, Gx, Gy, ref_l, pts, torch.as_tensor(K).double().cpu(), torch.as_tensor(R).double().cpu(),
+                               torch.as_tensor(t).double().cpu(), int(im_width), int(im_height))
+            R, t = self.forward_packed(prob, track=track)
+        return R, t
+
+    def multilevel_packed(self, levels, prob, track=False):
+        """multilevel_optimization over channel slices [(start, end), ...] on device-resident inputs
+        (an fmpnp_b200.Problem: HWC float32 maps); what the device-side adapter calls."""
+        R, t, r = self._run(prob, [(int(s), int(e)) for s, e in levels], track)
         if int(r["status"]) == _fm.STATUS_NO_INITIAL_COST:
             self.initial_cost_ = None
-            return R_init, t_init
+            return torch.from_numpy(prob.R0.reshape(3, 3).copy()), torch.from_numpy(prob.t0.copy())
         self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
         return R, t
+
+    def forward_packed(self, prob, track=False, select=None):
+        """forward() on device-resident inputs (an fmpnp_b200.Problem)."""
+        R_out, t_out, r = self._run(prob, None, track, select)
+        if self.initial_cost_ is None and int(r["best_num_inliers"]) >= 0:
+            self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
+        return R_out, t_out
 
     def compute_cost(self, pts3D, R, t, feature_map_query, feature_ref, K, im_width, im_height):
         """Mean of 0.5 * ||F[cell] - ref||^2 over the supported points (after the raw-SSD ratio
@@ -215,7 +265,4 @@ class sparseFeaturePnP(nn.Module):
         t = torch.tensor([1.0, 1.0, 0.0], dtype=torch.float64) if t_init is None else t_init
         prob = _problem(pts3D, feature_ref, feature_map_query, feature_grad_x, feature_grad_y, K, im_width, im_height,
                         R, t)
-        R_out, t_out, r = self._run(prob, None, track)
-        if self.initial_cost_ is None and int(r["best_num_inliers"]) >= 0:
-            self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
-        return R_out, t_out
+        return self.forward_packed(prob, track=track)

@@ -177,6 +177,32 @@ int fmpnp_find_inliers_batch(fmpnp_ctx *ctx, const fmpnp_problem *probs, int32_t
 int fmpnp_pack_chw_to_hwc(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, float *dst, int32_t C, int32_t Hf,
                           int32_t Wf, void *stream);
 
+/* Replaces `sobel_filter` (featurePnP/helpers/utils.py:81-104 = kornia.filters.spatial_gradient, called at
+ * s2dhm/pose_prediction/optimize_feature_pnp.py:31,61 and model.py:207) fused with the layout pack: one pass
+ * over a DEVICE CHW map (float32, or float64 if src_is_f64) writes the three DEVICE HWC float32 maps the
+ * refinement gathers from.  Gx = [[-1,0,1],[-2,0,2],[-1,0,1]] (x) F, Gy = transposed kernel, summed in
+ * float64.  border: FMPNP_BORDER_REPLICATE (kornia) or FMPNP_BORDER_ZERO (helpers/sobel_pytorch.py:41);
+ * normalized != 0 scales by 1/8 (newer kornia default; the reference's stored known answer needs 0). */
+enum { FMPNP_BORDER_REPLICATE = 0, FMPNP_BORDER_ZERO = 1 };
+int fmpnp_sobel_pack(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, float *F, float *Gx, float *Gy, int32_t C,
+                     int32_t Hf, int32_t Wf, int32_t border, int32_t normalized, void *stream);
+
+/* Replaces the reference-descriptor lookup of the adapter (optimize_feature_pnp.py:56):
+ * dst[n][c] = src[c][rows[n]][cols[n]].  src DEVICE CHW (float32 / float64), rows / cols DEVICE int32 [N]
+ * (negative indices wrap once, as torch indexing does), dst DEVICE [N][C] float32. */
+int fmpnp_gather_descriptors(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, const int32_t *rows,
+                             const int32_t *cols, float *dst, int32_t C, int32_t H, int32_t W, int32_t N, void *stream);
+
+/* Pyramid-level preparation of multilevel_optimization (model.py:196-200), DEVICE CHW in (float32 / float64),
+ * DEVICE CHW float64 out:
+ *   fmpnp_resize_bilinear_chw == nn.functional.interpolate(size=(Ho, Wo), mode='bilinear'), align_corners=False;
+ *   fmpnp_blur_chw            == depthwise conv2d with a DEVICE k x k float64 kernel and zero padding `pad`
+ *                                (the reference passes pad = 1 for every k): dst is (H+2pad-k+1) x (W+2pad-k+1). */
+int fmpnp_resize_bilinear_chw(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, double *dst, int32_t C, int32_t H,
+                              int32_t W, int32_t Ho, int32_t Wo, void *stream);
+int fmpnp_blur_chw(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, const double *kernel, double *dst, int32_t C,
+                   int32_t H, int32_t W, int32_t k, int32_t pad, void *stream);
+
 /* Number of kernels this context has launched so far (bench.py's `gpu_launches`). */
 int64_t fmpnp_launch_count(const fmpnp_ctx *ctx);
 
