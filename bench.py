@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--e2e-queries", type=int, default=32, help="queries per e2e step (host-resident inputs)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-adapter-e2e", action="store_true")
     ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
     ap.add_argument("--sort-points", action="store_true",
                     help="experiment: order each query's points by feature-map cell (DRAM page / TLB locality)")
@@ -373,6 +374,55 @@ def main():
                        "note": "HWC fp32 maps + descriptors + points in pinned host memory -> H2D -> find_inliers + "
                                "refine kernels -> result records D2H, all inside the timed region (PCIe-bound)"}
         del host, devbuf
+
+        # ---- e2e one level up (the reference's feature_pnp): hypercolumns in pinned host memory -> H2D ->
+        # Sobel + pack kernel, descriptor gather kernel -> the same refinement -> results D2H
+        if not args.no_adapter_e2e:
+            A = E
+            qh_host = [scenes[i].F.permute(2, 0, 1).contiguous().cpu().pin_memory() for i in range(A)]
+            pts_host = [scenes[i].pts3D.cpu().pin_memory() for i in range(A)]
+            cells = []
+            for i in range(A):  # reference keypoints: the ground-truth cell of every point in the query map
+                P = scenes[i].pts3D.cpu()
+                u = (scenes[i].K[0, 0] * P[:, 0] / P[:, 2] + scenes[i].K[0, 2]).clamp(0, 1023)
+                v = (scenes[i].K[1, 1] * P[:, 1] / P[:, 2] + scenes[i].K[1, 2]).clamp(0, 1023)
+                cells.append(((v.long() * args.map // 1024).int().to(dev), (u.long() * args.map // 1024).int().to(dev)))
+            qh_dev = [torch.empty_like(q, device=dev) for q in qh_host]
+            rh_dev = [torch.empty_like(q, device=dev) for q in qh_host]
+            pts_dev = [torch.empty_like(q, device=dev) for q in pts_host]
+            ares = torch.empty((A, RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
+            ares_host = torch.empty((A, RESULT_DTYPE.itemsize), dtype=torch.uint8).pin_memory()
+            a_h2d = sum(2 * q.numel() * 4 for q in qh_host) + sum(q.numel() * 8 for q in pts_host)
+
+            def adapter_step():
+                aprobs = []
+                for i in range(A):
+                    qh_dev[i].copy_(qh_host[i], non_blocking=True)
+                    rh_dev[i].copy_(qh_host[i], non_blocking=True)  # the reference image's hypercolumn
+                    pts_dev[i].copy_(pts_host[i], non_blocking=True)
+                    F_, Gx_, Gy_ = fm.sobel_pack(qh_dev[i], ctx=ctx)
+                    ref_ = fm.gather_descriptors(rh_dev[i], cells[i][0], cells[i][1], ctx=ctx)
+                    aprobs.append(fm.Problem(F_, Gx_, Gy_, ref_, pts_dev[i], scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024))
+                fm.refine_batch(aprobs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                                ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=ares)
+                ares_host.copy_(ares, non_blocking=True)
+
+            for _ in range(2):
+                adapter_step()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(ksteps):
+                adapter_step()
+            b.record()
+            torch.cuda.synchronize()
+            a_ms = a.elapsed_time(b)
+            line["e2e_adapter"] = {"value": A * ksteps / (a_ms / 1e3), "unit": UNIT + " per GPU", "h2d_bytes_per_step": int(a_h2d),
+                                   "d2h_bytes_per_step": int(ares_host.numel()), "queries_per_step": A,
+                                   "note": "feature_pnp level: query + reference hypercolumns (CHW fp32) and points in pinned "
+                                           "host memory -> H2D -> fmpnp_sobel_pack + fmpnp_gather_descriptors -> refinement "
+                                           "-> D2H; rank-local, not aggregated"}
+            del qh_host, qh_dev, rh_dev
 
     # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle port on a bounded sample
     if rank == 0 and world == 1 and not args.no_cpu:

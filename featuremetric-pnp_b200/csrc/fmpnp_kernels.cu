@@ -175,6 +175,43 @@ __device__ __forceinline__ void reduce_lanes(double (&a)[6]) {
     }
 }
 
+// Full-warp sum of the six per-point values with a halving butterfly: at distance 16 each lane keeps
+// three values and hands the other three to its partner, at 8 and 4 it keeps two, then one, and the
+// last two steps are a plain butterfly on that one value.  Every pairwise addition is the one the
+// straight butterfly (reduce_lanes<GRAD, 5>) performs, so the totals are bit-identical to it; it
+// just needs 8 additions and 16 shuffles instead of 30 and 60.  Afterwards the lanes with
+// (lane & 3) == 0 hold value number v = {0: a0, 4: a1, 8: a2, 12: 0, 16: a3, 20: a4, 24: a5, 28: 0}[lane].
+__device__ __forceinline__ double reduce_six(const double (&a)[6], int lane) {
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    double k0 = h16 ? a[3] : a[0], k1 = h16 ? a[4] : a[1], k2 = h16 ? a[5] : a[2];
+    const double s0 = h16 ? a[0] : a[3], s1 = h16 ? a[1] : a[4], s2 = h16 ? a[2] : a[5];
+    k0 = __dadd_rn(k0, shfl_xor_f64(s0, 16));
+    k1 = __dadd_rn(k1, shfl_xor_f64(s1, 16));
+    k2 = __dadd_rn(k2, shfl_xor_f64(s2, 16));
+    // distance 8: lanes with bit 3 clear keep (k0, k1), the others keep (k2, -)
+    double m0 = h8 ? k2 : k0, m1 = h8 ? 0.0 : k1;
+    const double t0 = h8 ? k0 : k2, t1 = h8 ? k1 : 0.0;
+    m0 = __dadd_rn(m0, shfl_xor_f64(t0, 8));
+    m1 = __dadd_rn(m1, shfl_xor_f64(t1, 8));
+    // distance 4: bit 2 clear keeps m0, set keeps m1
+    double v = h4 ? m1 : m0;
+    const double u = h4 ? m0 : m1;
+    v = __dadd_rn(v, shfl_xor_f64(u, 4));
+    v = __dadd_rn(v, shfl_xor_f64(v, 2));
+    v = __dadd_rn(v, shfl_xor_f64(v, 1));
+    return v;
+}
+
+// lane -> slot of the 6-double record it writes after reduce_six (or -1)
+__device__ __forceinline__ int six_slot(int lane) {
+    if (lane & 3) return -1;
+    const int g = lane >> 2;  // 0..7: (bit16, bit8, bit4)
+    // bit16 selects {a0,a1,a2} / {a3,a4,a5}; inside: g&3 == 0 -> first, 1 -> second (bit4), 2 -> third (bit8), 3 -> none
+    const int half = g >> 2, j = g & 3;
+    const int idx = j == 0 ? 0 : (j == 1 ? 1 : (j == 2 ? 2 : -1));
+    return idx < 0 ? -1 : half * 3 + idx;
+}
+
 template <bool GRAD>
 __device__ __forceinline__ void write_record(const double (&a)[6], double* rec_n) {
     double2* o = reinterpret_cast<double2*>(rec_n);
@@ -252,14 +289,17 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
             s[2] = baseGy + (size_t)cell * pitch + off;
         }
         dst += lane * 16;
+        const int full = nv >> 5, tail = nv & 31;  // whole 512-byte warp copies, then a partial one
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
-            const uint32_t d = dst + (uint32_t)(r * nv) * 16u;
-            if (SHORT) {  // nv <= 64
-                if (lane < nv) cp_async16_s(d, s[r]);
-                if (lane + 32 < nv) cp_async16_s(d + 512, s[r] + 512);
+            uint32_t d = dst + (uint32_t)(r * nv) * 16u;
+            const char* g = s[r];
+            if (SHORT) {  // nv <= 32
+                if (lane < nv) cp_async16_s(d, g);
             } else {
-                for (int v = lane; v < nv; v += 32) cp_async16_s(d + (uint32_t)(v - lane) * 16u, s[r] + (size_t)(v - lane) * 16);
+#pragma unroll 4
+                for (int i = 0; i < full; ++i, d += 512, g += 512) cp_async16_s(d, g);
+                if (lane < tail) cp_async16_s(d, g);
             }
         }
     };
@@ -314,8 +354,15 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
             for (int v = lane; v < nv; v += 32, p += 512) acc4<GRAD>(p, p + rowB, p + 2 * rowB, p + (ROWS - 1) * rowB, a);
             if (++cch == nCh) {
                 cch = 0;
-                reduce_lanes<GRAD, 5>(a);
-                if (lane == 0) write_record<GRAD>(a, c.rec + (size_t)bn[buf * 32 + ck] * kRecDoubles);
+                double* rec_n = c.rec + (size_t)bn[buf * 32 + ck] * kRecDoubles;
+                if (GRAD) {
+                    const double v = reduce_six(a, lane);
+                    const int slot = six_slot(lane);
+                    if (slot >= 0) rec_n[slot] = v;
+                } else {
+                    reduce_lanes<GRAD, 5>(a);
+                    if (lane == 0) rec_n[0] = a[0];
+                }
                 ++ck;
             }
         }

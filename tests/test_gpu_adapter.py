@@ -211,3 +211,50 @@ def test_resampled_pyramid_matches_reference(name):
     # resized / blurred maps are float64 in the reference and float32 in HBM: BASELINE bars, not the tight ones
     check_track(name, m, g, COST_RTOL)
     assert rot_angle_deg(R.numpy(), g["out_R"]) <= ROT_TOL_DEG and np.abs(t.numpy() - g["out_t"]).max() <= TRANS_TOL_M
+
+
+# ----------------------------------------------------------------------------------------------
+# --only_optimization replay: one batched launch over the cached predictions == per-query feature_pnp
+# ----------------------------------------------------------------------------------------------
+def test_replay_batch_equals_per_query_adapter(tmp_path, monkeypatch):
+    import model
+    from pose_prediction import optimize_feature_pnp as adapter
+    from pose_prediction import replay
+    names = ["adapter_pnp_exact", "adapter_pnp_float", "adapter_multi_mask"]
+    gs = {n: load(n) for n in names}
+    records, hcs = {}, {}
+    for n, g in gs.items():
+        N = g["points_3d"].shape[0]
+        records["q_%s.jpg:r_%s.jpg" % (n, n)] = {
+            "reference_filename": "r_%s.jpg" % n, "success": True, "query_2D": np.zeros((N, 2)),
+            "reference_2D": g["reference_inliers"], "points_3D": g["points_3d"], "num_matches": N, "num_inliers": N,
+            "inlier_mask": np.arange(N), "quaternion": np.array([1.0, 0.0, 0.0, 0.0]), "matrix": g["matrix"]}
+        hcs["q_%s.jpg" % n], hcs["r_%s.jpg" % n] = torch.from_numpy(g["qh"]).cuda(), torch.from_numpy(g["rh"]).cuda()
+    failed = dict(records["q_adapter_pnp_exact.jpg:r_adapter_pnp_exact.jpg"], success=False)
+    records["q_failed.jpg"] = failed
+    out = str(tmp_path) + os.sep
+    replay.write_npz(out + "cached_matches/slice.npz", records)
+    back = replay.read_npz(out)
+    rows, poses = replay.refine_cached(back, lambda f: hcs[f], lambda q: gs[names[0]]["K"], [256, 256], n_iters=7,
+                                       loss_fn="geman_mcclure_loss", lambda_=0.01)
+    assert len(rows) == 4 and len(poses) == 8
+    monkeypatch.setattr(adapter, "sparseFeaturePnP", functools.partial(
+        model.sparseFeaturePnP, n_iters=7, loss_fn=__import__("helpers.utils").utils.geman_mcclure_loss, lambda_=0.01))
+    for i, n in enumerate(names):
+        g = gs[n]
+        R, t, m = adapter.feature_pnp(hcs["q_%s.jpg" % n], hcs["r_%s.jpg" % n],
+                                      replay.prediction_from_record(back["q_%s.jpg:r_%s.jpg" % (n, n)]),
+                                      torch.from_numpy(g["K"]), [256, 256])
+        row, pose = rows[i], poses[2 * i + 1]
+        assert row[0] == "r_%s.jpg" % n and row[1] == "q_%s.jpg" % n and row[2] == g["points_3d"].shape[0]
+        assert row[3] == m.best_num_inliers_ and row[4] == m.initial_cost_.item() and row[5] == m.best_cost_.item()
+        assert np.array_equal(np.array(pose[5:]), t.numpy())  # same kernel, same reduction order: bit-identical
+        T = np.eye(4)
+        T[:3, :3] = R.numpy()
+        from pose_prediction import matrix_utils
+        assert np.array_equal(np.array(pose[1:5]), matrix_utils.matrix_quaternion(T))
+    assert rows[3][2:] == [None] * 5 and poses[6] == poses[7]
+    replay.write_summary(out + "featurePnP_summary.csv", rows)
+    replay.write_poses(out + "poses.txt", poses)
+    assert len(open(out + "featurePnP_summary.csv").read().splitlines()) == 5
+    assert len(open(out + "poses.txt").read().splitlines()) == 4
