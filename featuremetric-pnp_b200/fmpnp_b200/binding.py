@@ -154,6 +154,8 @@ _default_ctx = {}
 
 
 def default_context(device=None):
+    if not torch.cuda.is_available():
+        raise FmpnpError("no CUDA device: the feature-metric PnP refinement has no CPU fallback")
     dev = torch.cuda.current_device() if device is None else (torch.device(device).index or 0)
     if dev not in _default_ctx:
         _default_ctx[dev] = Context(dev)

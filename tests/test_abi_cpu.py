@@ -53,6 +53,16 @@ def test_no_cpu_fallback():
     with pytest.raises(fm.FmpnpError):
         m(torch.zeros(4, 3, dtype=torch.float64), torch.zeros(4, 2), torch.zeros(2, 8, 8), torch.zeros(2, 8, 8),
           torch.zeros(2, 8, 8), torch.eye(3, dtype=torch.float64), 64, 64)
+    # the device-side adapter and its kernels have no CPU path either
+    from collections import namedtuple
+    from pose_prediction import optimize_feature_pnp as adapter
+    P = namedtuple("P", "points_3d reference_inliers matrix")
+    with pytest.raises(fm.FmpnpError):
+        adapter.build_problem(torch.zeros(1, 2, 8, 8), torch.zeros(1, 2, 8, 8),
+                              P(torch.zeros(4, 3).numpy(), torch.zeros(4, 2).numpy(), torch.eye(4).numpy()),
+                              torch.eye(3), [64, 64])
+    with pytest.raises(fm.FmpnpError):
+        fm.sobel_pack(torch.zeros(2, 8, 8))
 
 
 def test_loss_mapping():
