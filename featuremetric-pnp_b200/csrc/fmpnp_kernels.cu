@@ -92,7 +92,8 @@ struct EvalCtx {
     int32_t L;                         // lanes sharing one point when a whole point is one item (nCh == 1)
     int32_t n0, n1;                    // this CTA's share of the points: [n0, n1)
     int32_t range_len;                 // points per fixed reduction range (kRanges ranges cover N)
-    int32_t csize, crank;              // thread-block cluster working on this query
+    int32_t csize, crank;              // thread-block cluster working on this query (or: tasks of this evaluation)
+    double* part_out;                  // task scheduler: this task's partial sums go here (global), no combine
 };
 
 // Staging geometry of one evaluation.
@@ -561,8 +562,8 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         double m = -INFINITY;
         int nanf = 0;
         for (int n = c.n0 + tid; n < c.n1; n += kThreads) {
-            if (!c.supp[n]) continue;
-            const double x = __dmul_rn(0.5, c.rec[(size_t)n * kRecDoubles]);
+            if (!__ldcg(c.supp + n)) continue;  // .cg: records may have been written by another CTA (task scheduler)
+            const double x = __dmul_rn(0.5, __ldcg(c.rec + (size_t)n * kRecDoubles));
             double rho = x, w = 1.0;
             if (c.ratio_mode == 1) robust_loss(c.loss_id, c.alpha, x, rho, w);
             const double a = fabs(rho);
@@ -613,12 +614,12 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         for (int i = 0; i < 28; ++i) acc[i] = 0.0;
         int32_t cnt[2] = {0, 0};  // survivors, supported
         for (int n = r0 + tid; n < r1; n += kThreads) {
-            const bool sup = c.supp[n] != 0;
+            const bool sup = __ldcg(c.supp + n) != 0;
             bool keep = false;
             if (sup) {
                 ++cnt[1];
                 const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
-                const double2 rc0 = r[0];
+                const double2 rc0 = __ldcg(r);
                 const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
                 double rho = x, w = 1.0;
                 if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
@@ -627,7 +628,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
                     ++cnt[0];
                     acc[27] = __dadd_rn(acc[27], rho);
                     if (GRAD) {
-                        const double2 rc1 = r[1], rc2 = r[2];
+                        const double2 rc1 = __ldcg(r + 1), rc2 = __ldcg(r + 2);
                         const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
                                                       q.im_w, q.im_h);
                         contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
@@ -655,7 +656,9 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
                 }
                 sh.tree[level][i] = x;
                 if (rr == r_count - 1) {  // r_count is a power of two: the total sits on top of the stack
-                    if (c.csize > 1)
+                    if (c.part_out)
+                        c.part_out[i] = x;
+                    else if (c.csize > 1)
                         sh.cpart[rp.cpar][i] = x;
                     else
                         sh.ev[i] = x;
@@ -664,6 +667,11 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         }
     }
     int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
+    if (c.part_out) {  // the CTA that completes the evaluation combines the tasks' partials (combine_parts)
+        if (warp == 0 && lane < 2) reinterpret_cast<long long*>(c.part_out)[28 + lane] = tot_i;
+        __syncthreads();
+        return;
+    }
     if (warp == 0 && lane < 2) {
         if (c.csize > 1)
             sh.cpart_i[rp.cpar][lane] = tot_i;
@@ -806,6 +814,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.min_depth = p.min_depth;
         c.csize = csize;
         c.crank = crank;
+        c.part_out = nullptr;
         {
             const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
             c.range_len = per;
@@ -1014,6 +1023,486 @@ __global__ void __launch_bounds__(kThreads, 2) find_inliers_kernel(const LaunchP
 }
 
 // ---------------------------------------------------------------------------------------------
+// Task scheduler (LaunchParams::scheduler == 1).
+// One evaluation of a query = `units` tasks, each a contiguous run of the 16 fixed point ranges.  Tasks sit
+// in one global FIFO (ticket queue: a consumer takes a ticket and waits for that position to be filled).
+// The CTA that completes the last task of an evaluation reduces ALL the per-point records of the query
+// (same fixed-order tree as above: bit-identical to the one-CTA-per-query path), runs the solve / accept /
+// reject step on the query's state (kept in global memory between evaluations) and queues the tasks of the
+// next evaluation.  Any number of queries keeps every CTA busy: no waves, no tail, no idle slots.
+// ---------------------------------------------------------------------------------------------
+constexpr unsigned long long kQueueEmpty = ~0ull;
+constexpr int kPartStride = 32;  // doubles per task partial: 28 sums, 2 counts (as int64), 2 unused
+constexpr unsigned long long kWaitLimitNs = 20ull * 1000 * 1000 * 1000;  // then the kernel gives up instead of hanging
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+__device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) {
+    return *reinterpret_cast<const volatile unsigned int*>(p);
+}
+
+// thread 0 only: queues the `units` tasks of query q's next evaluation (its state is already in global memory)
+__device__ __forceinline__ void enqueue_evaluation(const SchedDev& s, int q) {
+    __threadfence();  // state (and, for the finisher, everything before) visible before the tasks are
+    const unsigned int base = atomicAdd(s.tail, (unsigned int)s.units);
+    for (int u = 0; u < s.units; ++u) {
+        const unsigned int pos = base + (unsigned int)u;
+        const unsigned long long v = ((unsigned long long)pos << 32) | (unsigned int)(q * kRanges + u + 1);
+        *reinterpret_cast<volatile unsigned long long*>(&s.queue[pos & (s.cap - 1)]) = v;
+    }
+}
+
+// thread 0 only: next task id (q * kRanges + u), or -1 when every query is finished (or on a protocol error)
+__device__ __forceinline__ int dequeue_task(const SchedDev& s, int B) {
+    const unsigned int ticket = atomicAdd(s.head, 1u);
+    const unsigned long long* slot = &s.queue[ticket & (s.cap - 1)];
+    unsigned long long t0 = 0;
+    for (uint32_t spin = 0;; ++spin) {
+        const unsigned long long v = ld_volatile_u64(slot);
+        if (v != kQueueEmpty && (unsigned int)(v >> 32) == ticket) {
+            __threadfence();
+            return (int)(unsigned int)(v & 0xffffffffu) - 1;
+        }
+        if (ld_volatile_u32(s.done) >= (unsigned int)B || ld_volatile_u32(s.error) != 0u) return -1;
+        if ((spin & 1023u) == 1023u) {
+            const unsigned long long now = global_timer_ns();
+            if (t0 == 0) t0 = now;
+            if (now - t0 > kWaitLimitNs) {
+                atomicExch(s.error, 1u);
+                return -1;
+            }
+        }
+        __nanosleep(200);
+    }
+}
+
+// thread 0: query state global <-> shared
+__device__ __forceinline__ void load_state(Shared& sh, const volatile QueryState& g) {  // volatile: L1 may hold a stale copy
+    for (int i = 0; i < 9; ++i) {
+        sh.R[i] = g.R[i];
+        sh.Rn[i] = g.Rn[i];
+        sh.Rb[i] = g.Rb[i];
+    }
+    for (int i = 0; i < 3; ++i) {
+        sh.t[i] = g.t[i];
+        sh.tn[i] = g.tn[i];
+        sh.tb[i] = g.tb[i];
+    }
+    for (int i = 0; i < 27; ++i) sh.lin[i] = g.lin[i];
+    sh.prev_cost = g.prev_cost;
+    sh.best_cost = g.best_cost;
+    sh.lambda = g.lambda;
+    sh.lr = g.lr;
+    sh.initial_cost = g.initial_cost;
+    sh.gathered = g.gathered;
+    sh.best_n = g.best_n;
+    sh.has_best = g.has_best;
+    sh.status = g.status;
+    sh.flag = g.flag;
+    sh.hist_len = g.hist_len;
+    sh.n_evals = g.n_evals;
+    sh.initial_set = g.initial_set;
+    for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) sh.level_status[i] = g.level_status[i];
+}
+
+__device__ __forceinline__ void store_state(const Shared& sh, QueryState& g) {
+    for (int i = 0; i < 9; ++i) {
+        g.R[i] = sh.R[i];
+        g.Rn[i] = sh.Rn[i];
+        g.Rb[i] = sh.Rb[i];
+    }
+    for (int i = 0; i < 3; ++i) {
+        g.t[i] = sh.t[i];
+        g.tn[i] = sh.tn[i];
+        g.tb[i] = sh.tb[i];
+    }
+    for (int i = 0; i < 27; ++i) g.lin[i] = sh.lin[i];
+    g.prev_cost = sh.prev_cost;
+    g.best_cost = sh.best_cost;
+    g.lambda = sh.lambda;
+    g.lr = sh.lr;
+    g.initial_cost = sh.initial_cost;
+    g.gathered = sh.gathered;
+    g.best_n = sh.best_n;
+    g.has_best = sh.has_best;
+    g.status = sh.status;
+    g.flag = sh.flag;
+    g.hist_len = sh.hist_len;
+    g.n_evals = sh.n_evals;
+    g.initial_set = sh.initial_set;
+    for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) g.level_status[i] = sh.level_status[i];
+}
+
+// describes the next evaluation of a query in its global state (thread 0)
+__device__ __forceinline__ void describe_evaluation(QueryState& g, const double* R, const double* t, int phase, int grad,
+                                                    int c0, int Cl, int ratio_mode, int loss, int hist_entry, int units) {
+    for (int i = 0; i < 9; ++i) g.evR[i] = R[i];
+    for (int i = 0; i < 3; ++i) g.evt[i] = t[i];
+    g.phase = phase;
+    g.ev_grad = grad;
+    g.ev_c0 = c0;
+    g.ev_Cl = Cl;
+    g.ev_ratio_mode = ratio_mode;
+    g.ev_loss = loss;
+    g.ev_hist = hist_entry;
+    g.pending = units;
+}
+
+// Adds the partial sums the `units` tasks of an evaluation left in global memory, in the order
+// cluster_combine uses (pairwise tree over the tasks): sh.ev[0..27], ev_count, ev_nsup, ev_cost.
+__device__ __forceinline__ void combine_parts(Shared& sh, const double* part, int units) {
+    const int tid = threadIdx.x;
+    if (tid < 28) {
+        double v[kRanges];
+#pragma unroll
+        for (int r = 0; r < kRanges; ++r) v[r] = r < units ? __ldcg(part + r * kPartStride + tid) : 0.0;
+#pragma unroll
+        for (int w = 1; w < kRanges; w <<= 1) {
+            if (w < units) {
+#pragma unroll
+                for (int i = 0; i + w < kRanges; i += 2 * w) v[i] = __dadd_rn(v[i], v[i + w]);
+            }
+        }
+        sh.ev[tid] = v[0];
+    } else if (tid >= 32 && tid < 34) {
+        long long s = 0;
+        for (int r = 0; r < units; ++r) s += __ldcg(reinterpret_cast<const long long*>(part + r * kPartStride) + 28 + (tid - 32));
+        (&sh.ev_count)[tid - 32] = (int32_t)s;
+    }
+    __syncthreads();
+    if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;
+    __syncthreads();
+}
+
+template <int MODE>
+__device__ __forceinline__ void task_body(const LaunchParams& p) {
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ Shared sh;
+    __shared__ double evpose[12];
+    __shared__ int32_t s_task, s_last;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const SchedDev& sc = p.sched;
+    RingPos rp;
+    rp.pos = 0;
+    rp.bits = 0;
+    rp.cpar = 0;
+
+    // ---- every CTA starts a share of the queries: initial state + the tasks of their first evaluation
+    if (tid == 0) {
+        for (int q = blockIdx.x; q < p.B; q += gridDim.x) {
+            const QueryDev& qd = p.queries[q];
+            QueryState& g = sc.states[q];
+            for (int i = 0; i < 9; ++i) g.R[i] = g.Rn[i] = g.Rb[i] = qd.R0[i];
+            for (int i = 0; i < 3; ++i) g.t[i] = g.tn[i] = g.tb[i] = qd.t0[i];
+            for (int i = 0; i < 27; ++i) g.lin[i] = 0.0;
+            g.prev_cost = g.best_cost = NAN;
+            g.lambda = p.lambda0;
+            g.lr = 1.0;
+            g.initial_cost = NAN;
+            g.gathered = 0;
+            g.best_n = -1;
+            g.has_best = 0;
+            g.status = FMPNP_STATUS_OK;
+            g.flag = 0;
+            g.hist_len = 0;
+            g.n_evals = 0;
+            g.initial_set = 0;
+            for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) g.level_status[i] = 0;
+            g.level = 0;
+            g.it = 0;
+            if (MODE == kModeRefine) p.results[q].status = FMPNP_STATUS_INCOMPLETE;
+            if (MODE == kModeComputeCost)
+                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+            else if (MODE == kModeFindInliers)
+                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, sc.units);
+            else if (p.n_levels > 0)  // multilevel: compute_cost on ALL channels first (model.py:182)
+                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+            else
+                describe_evaluation(g, qd.R0, qd.t0, kPhaseFirst, 1, 0, qd.C, p.use_ratio ? 1 : 0, p.loss_id, 0, sc.units);
+            enqueue_evaluation(sc, q);
+        }
+    }
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_task = dequeue_task(sc, p.B);
+        __syncthreads();
+        const int task = s_task;
+        if (task < 0) break;
+        const int qi = task / kRanges, u = task - qi * kRanges;
+        const QueryDev& q = p.queries[qi];
+        QueryState& g = sc.states[qi];
+        const volatile QueryState& gv = g;
+        if (tid < 9) evpose[tid] = gv.evR[tid];
+        if (tid >= 9 && tid < 12) evpose[tid] = gv.evt[tid - 9];
+
+        EvalCtx c;
+        c.q = &q;
+        c.rec = p.rec + (size_t)qi * p.n_max * kRecDoubles;
+        c.supp = p.supp + (size_t)qi * p.n_max;
+        c.ring = ring;
+        c.ring_per_warp = p.ring_per_warp;
+        c.min_depth = p.min_depth;
+        c.csize = 1;
+        c.crank = 0;
+        c.part_out = nullptr;
+        c.c0 = gv.ev_c0;
+        c.Cl = gv.ev_Cl;
+        c.loss_id = gv.ev_loss;
+        c.alpha = p.alpha;
+        c.ratio_mode = gv.ev_ratio_mode;
+        c.thr = p.ratio_thr;
+        const bool grad = gv.ev_grad != 0;
+        const int hist_entry = gv.ev_hist;
+        c.aligned = slice_aligned(q, c.c0, c.Cl, grad);
+        c.inl_out = MODE == kModeFindInliers ? p.inliers_out + (size_t)qi * p.inliers_stride : nullptr;
+        c.h_px = nullptr;
+        c.h_mask = nullptr;
+        c.h_kept = nullptr;
+        if (hist_entry >= 0) hist_slices(p, qi, hist_entry, c);
+        {
+            const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
+            const int rpu = kRanges / sc.units;  // fixed ranges per task
+            c.range_len = per;
+            c.n0 = min(q.N, u * rpu * per);
+            c.n1 = min(q.N, (u + 1) * rpu * per);
+        }
+        __syncthreads();
+
+        // ---- the task: stream this run of points, one record per supported point
+        rp.pos = 0;
+        if (grad) {
+            set_geometry(c, 4);
+            stream_points<true>(c, evpose, evpose + 9, sh, rp);
+        } else {
+            set_geometry(c, 2);
+            stream_points<false>(c, evpose, evpose + 9, sh, rp);
+        }
+        __syncthreads();
+        // Without a ratio test the per-point phase needs nothing from the other tasks: this task sums its own
+        // ranges and leaves 28 + 2 partials.  With one, the limit is a maximum over ALL points, so the CTA
+        // that completes the evaluation runs the per-point phase over the whole query.
+        const bool split = c.ratio_mode == 0 && sc.units > 1;
+        double* const parts = sc.part + (size_t)qi * kRanges * kPartStride;
+        if (split) {
+            c.csize = sc.units;
+            c.crank = u;
+            c.part_out = parts + u * kPartStride;
+            if (grad)
+                reduce_points<true>(c, evpose, evpose + 9, sh, rp);
+            else
+                reduce_points<false>(c, evpose, evpose + 9, sh, rp);
+            c.csize = 1;
+            c.crank = 0;
+            c.part_out = nullptr;
+        }
+        if (tid == 0) {
+            __threadfence();  // records / partials before the count
+            s_last = atomicSub(&g.pending, 1) == 1;
+            if (s_last) __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) continue;
+
+        // ---- this CTA completed the evaluation: total the query, advance its state machine
+        c.n0 = 0;
+        c.n1 = q.N;
+        if (tid == 0) load_state(sh, gv);
+        __syncthreads();
+        if (split)
+            combine_parts(sh, parts, sc.units);
+        else if (grad)
+            reduce_points<true>(c, evpose, evpose + 9, sh, rp);
+        else
+            reduce_points<false>(c, evpose, evpose + 9, sh, rp);
+        if (tid == 0) {
+            sh.n_evals += 1;
+            sh.gathered += (long long)sh.ev_nsup * c.Cl * (grad ? 4 : 2);
+        }
+        __syncthreads();
+
+        bool finished = false, have_eval = false;
+        int lvl = gv.level, it = gv.it;
+        const int phase = gv.phase;
+        enum { kStartLevel, kTryStep, kFinishLevel } next = kStartLevel;
+
+        if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
+            if (tid == 0) {
+                p.cost_out[qi] = sh.ev_nsup > 0 ? sh.ev_cost : NAN;
+                if (p.nsup_out) p.nsup_out[qi] = sh.ev_nsup;
+            }
+            finished = true;
+        } else if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152): the mask was written by reduce_points
+            finished = true;
+        } else if (phase == kPhaseCost) {
+            if (sh.ev_nsup == 0) {  // compute_cost is None -> return the initial pose (model.py:183-187)
+                if (tid == 0) sh.status = FMPNP_STATUS_NO_INITIAL_COST;
+                finished = true;
+            } else {
+                if (tid == 0) {
+                    sh.initial_cost = sh.ev_cost;
+                    sh.initial_set = 1;
+                }
+                lvl = 0;
+                next = kStartLevel;
+            }
+        } else if (phase == kPhaseFirst) {  // i == 0 of a level (model.py:303-359)
+            if (sh.ev_nsup == 0) {          // model.py:316-320 -> forward returns the CURRENT pose
+                if (tid == 0) {
+                    sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                    sh.level_status[lvl] = FMPNP_STATUS_EMPTY_SUPPORT;
+                }
+                ++lvl;
+                next = kStartLevel;
+                finished = lvl >= (p.n_levels > 0 ? p.n_levels : 1);
+            } else {
+                if (tid == 0) {
+                    sh.prev_cost = sh.ev_cost;
+                    sh.best_cost = sh.ev_cost;
+                    sh.best_n = sh.ev_count;
+                    sh.has_best = 1;
+                    for (int i = 0; i < 9; ++i) sh.Rb[i] = sh.R[i];
+                    for (int i = 0; i < 3; ++i) sh.tb[i] = sh.t[i];
+                    if (!sh.initial_set) {  // `if self.initial_cost_ is None` (model.py:355-356)
+                        sh.initial_cost = sh.ev_cost;
+                        sh.initial_set = 1;
+                    }
+                    for (int i = 0; i < 27; ++i) sh.lin[i] = sh.ev[i];
+                    sh.lambda = p.lambda0;  // model.py:281
+                    sh.lr = 1.0;
+                    sh.status = FMPNP_STATUS_OK;
+                    sh.flag = 0;
+                    hist_record(p, qi, sh.hist_len, sh.R, sh.t, sh.ev_cost);
+                    sh.hist_len += 1;
+                }
+                it = 0;
+                next = kTryStep;
+            }
+        } else {  // trial pose evaluated (model.py:428-486)
+            if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
+                if (tid == 0) {
+                    sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                    sh.flag = 2;
+                }
+                next = kFinishLevel;
+            } else {
+                if (tid == 0) {
+                    const double new_cost = sh.ev_cost;
+                    hist_record(p, qi, sh.hist_len, sh.Rn, sh.tn, new_cost);  // model.py:464-465
+                    sh.hist_len += 1;
+                    const bool worse = new_cost > sh.prev_cost;
+                    {  // model.py:469-470
+                        const double l = __dmul_rn(sh.lambda, worse ? 10.0 : 0.1);
+                        sh.lambda = l < 1e-6 ? 1e-6 : (l > 1e4 ? 1e4 : l);
+                    }
+                    if (worse) {  // model.py:472-476: reject, keep (R, t) and its linearisation
+                        const double l = __dmul_rn(0.1, sh.lr);
+                        sh.lr = l < 1e-3 ? 1e-3 : (l > 1.0 ? 1.0 : l);
+                    } else {  // model.py:477-486: accept
+                        sh.lr = 1.0;
+                        if (new_cost < sh.best_cost) {
+                            for (int i = 0; i < 9; ++i) sh.Rb[i] = sh.Rn[i];
+                            for (int i = 0; i < 3; ++i) sh.tb[i] = sh.tn[i];
+                            sh.best_n = sh.ev_count;
+                            sh.best_cost = new_cost;
+                        }
+                        sh.prev_cost = new_cost;
+                        for (int i = 0; i < 9; ++i) sh.R[i] = sh.Rn[i];
+                        for (int i = 0; i < 3; ++i) sh.t[i] = sh.tn[i];
+                        for (int i = 0; i < 27; ++i) sh.lin[i] = sh.ev[i];
+                    }
+                }
+                ++it;
+                next = kTryStep;
+            }
+        }
+
+        const int nlev = p.n_levels > 0 ? p.n_levels : 1;
+        while (!finished && !have_eval) {
+            __syncthreads();
+            if (next == kStartLevel) {
+                if (tid == 0) {
+                    const int c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
+                    const int Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
+                    describe_evaluation(g, sh.R, sh.t, kPhaseFirst, 1, c0, Cl, p.use_ratio ? 1 : 0, p.loss_id, sh.hist_len,
+                                        sc.units);
+                }
+                have_eval = true;
+            } else if (next == kTryStep) {
+                if (it >= p.n_iters) {
+                    next = kFinishLevel;
+                    continue;
+                }
+                if (warp == 0) solve_and_update(sh, p.solver, lane);
+                __syncthreads();
+                if (sh.flag == 1) {  // NaN step: leave the loop, best pose (model.py:411-413)
+                    __syncthreads();
+                    if (tid == 0) sh.status = FMPNP_STATUS_NAN_STEP;
+                    next = kFinishLevel;
+                    continue;
+                }
+                if (tid == 0)
+                    describe_evaluation(g, sh.Rn, sh.tn, kPhaseTrial, 1, gv.ev_c0, gv.ev_Cl, p.use_ratio ? 1 : 0, p.loss_id,
+                                        sh.hist_len, sc.units);
+                have_eval = true;
+            } else {  // kFinishLevel (model.py:491-494): best pose unless the loop was left on an empty support
+                if (tid == 0) {
+                    if (sh.flag != 2) {
+                        for (int i = 0; i < 9; ++i) sh.R[i] = sh.Rb[i];
+                        for (int i = 0; i < 3; ++i) sh.t[i] = sh.tb[i];
+                    }
+                    sh.level_status[lvl] = sh.status;
+                    sh.flag = 0;
+                }
+                ++lvl;
+                next = kStartLevel;
+                finished = lvl >= nlev;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (finished) {
+                if (MODE == kModeRefine) {
+                    fmpnp_result& r = p.results[qi];
+                    for (int i = 0; i < 9; ++i) r.R[i] = sh.R[i];
+                    for (int i = 0; i < 3; ++i) r.t[i] = sh.t[i];
+                    r.best_cost = sh.best_cost;
+                    r.initial_cost = sh.initial_cost;
+                    r.best_num_inliers = sh.best_n;
+                    r.status = sh.status;
+                    r.n_evaluations = sh.n_evals;
+                    for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) r.level_status[i] = sh.level_status[i];
+                    r.gathered_rows = sh.gathered;
+                    if (p.hist.enabled) p.hist.len[qi] = sh.hist_len;
+                }
+                __threadfence();
+                atomicAdd(sc.done, 1u);
+            } else {
+                store_state(sh, g);
+                g.level = lvl;
+                g.it = it;
+                enqueue_evaluation(sc, qi);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) refine_tasks_kernel(const LaunchParams p) { task_body<kModeRefine>(p); }
+__global__ void __launch_bounds__(kThreads, 2) compute_cost_tasks_kernel(const LaunchParams p) {
+    task_body<kModeComputeCost>(p);
+}
+__global__ void __launch_bounds__(kThreads, 2) find_inliers_tasks_kernel(const LaunchParams p) {
+    task_body<kModeFindInliers>(p);
+}
+
+// ---------------------------------------------------------------------------------------------
 // CHW (float32 / float64) -> HWC float32 pack: a (C) x (Hf*Wf) transpose through shared memory.
 // ---------------------------------------------------------------------------------------------
 template <typename T>
@@ -1042,7 +1531,7 @@ cudaError_t launch_pack_chw_to_hwc(const void* src, int src_is_f64, float* dst, 
     return cudaGetLastError();
 }
 
-size_t refine_static_smem_bytes() { return sizeof(Shared); }
+size_t refine_static_smem_bytes() { return sizeof(Shared) + 128; }
 
 cudaError_t refine_set_max_dynamic_smem(int bytes) {
     cudaError_t e = cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
@@ -1050,6 +1539,9 @@ cudaError_t refine_set_max_dynamic_smem(int bytes) {
         e = cudaFuncSetAttribute(compute_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(find_inliers_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(refine_tasks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(compute_cost_tasks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(find_inliers_tasks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     return e;
 }
 
@@ -1061,7 +1553,14 @@ cudaError_t refine_allow_nonportable_clusters(int allow) {
     return e;
 }
 
-static void (*kernel_of(int mode))(LaunchParams) {
+static void (*kernel_of(int mode, int scheduler))(LaunchParams) {
+    if (scheduler == 1) {
+        switch (mode) {
+            case kModeComputeCost: return compute_cost_tasks_kernel;
+            case kModeFindInliers: return find_inliers_tasks_kernel;
+            default: return refine_tasks_kernel;
+        }
+    }
     switch (mode) {
         case kModeComputeCost: return compute_cost_kernel;
         case kModeFindInliers: return find_inliers_kernel;
@@ -1083,7 +1582,7 @@ cudaError_t launch_refine(const LaunchParams& p, int grid, int ring_bytes, cudaS
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = p.cluster_size > 1 ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kernel_of(p.mode), p);
+    return cudaLaunchKernelEx(&cfg, kernel_of(p.mode, p.scheduler), p);
 }
 
 // how many clusters of `cluster_size` CTAs (each with ring_bytes of dynamic shared memory) can be

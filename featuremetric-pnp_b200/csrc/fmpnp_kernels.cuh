@@ -39,6 +39,41 @@ struct HistoryDev {
     uint8_t* kept;
 };
 
+// ---------------------------------------------------------------------------------------------
+// Task scheduler.  An evaluation of a query is cut into `units` point ranges; CTAs pull units from one
+// global FIFO, the CTA that finishes the last unit of an evaluation reduces the per-point records,
+// advances the query's LM state machine and queues the units of its next evaluation.
+// ---------------------------------------------------------------------------------------------
+enum TaskPhase { kPhaseCost = 0, kPhaseFirst = 1, kPhaseTrial = 2 };
+
+struct __align__(16) QueryState {
+    double R[9], t[3];    // current pose (last accepted)
+    double Rn[9], tn[3];  // trial pose
+    double Rb[9], tb[3];  // best pose
+    double lin[27];       // accepted linearisation
+    double prev_cost, best_cost, lambda, lr, initial_cost;
+    double evR[9], evt[3];  // pose of the evaluation in flight
+    long long gathered;
+    int32_t best_n, has_best, status, flag, hist_len, n_evals, initial_set;
+    int32_t level_status[FMPNP_MAX_LEVELS];
+    int32_t phase, level, it;
+    int32_t ev_grad, ev_c0, ev_Cl, ev_ratio_mode, ev_loss, ev_hist;  // the evaluation in flight
+    int32_t pending;      // its units still running
+    int32_t pad;
+};
+
+struct SchedDev {
+    unsigned long long* queue;  // [cap] entries (position << 32 | unit + 1), 0xff.. = empty
+    unsigned int* head;         // next ticket
+    unsigned int* tail;         // next position to fill
+    unsigned int* done;         // finished queries
+    unsigned int* error;        // watchdog / protocol error flag
+    uint32_t cap;               // power of two
+    int32_t units;              // units per evaluation: 1, 2, 4, 8 or 16
+    QueryState* states;         // [B]
+    double* part;               // [B][16][32] partial sums of the tasks of the evaluation in flight
+};
+
 struct LaunchParams {
     const QueryDev* queries;
     int32_t B;
@@ -63,6 +98,8 @@ struct LaunchParams {
     int32_t ring_per_warp;  // bytes of the shared-memory ring owned by one warp
     int32_t min_depth;      // minimum slots per warp
     int32_t cluster_size;   // CTAs per query (thread-block cluster); grid = clusters * cluster_size
+    SchedDev sched;         // task scheduler (scheduler == 1): rec / supp are then per QUERY, not per CTA
+    int32_t scheduler;      // 0: one CTA (or cluster) per query, 1: task queue
 };
 
 // Host-side launchers (defined in fmpnp_kernels.cu)

@@ -79,7 +79,7 @@ def lib():
             L.fmpnp_launch_count.argtypes = [C.c_void_p]
             L.fmpnp_launch_count.restype = C.c_int64
             L.fmpnp_last_geometry.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
-                                              C.POINTER(C.c_int32)]
+                                              C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
             L.fmpnp_last_geometry.restype = C.c_int
             L.fmpnp_refine_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.POINTER(COptions),
                                              C.c_void_p, C.POINTER(CHistory), C.c_void_p]
@@ -145,9 +145,9 @@ class Context:
     @property
     def last_geometry(self):
         """(CTAs in the grid, CTAs per query, staging-ring bytes per CTA) of the last launch."""
-        g, c, r = C.c_int32(), C.c_int32(), C.c_int32()
-        lib().fmpnp_last_geometry(self._h, C.byref(g), C.byref(c), C.byref(r))
-        return dict(grid=g.value, cluster_size=c.value, ring_bytes=r.value)
+        g, c, r, u = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        lib().fmpnp_last_geometry(self._h, C.byref(g), C.byref(c), C.byref(r), C.byref(u))
+        return dict(grid=g.value, cluster_size=c.value, ring_bytes=r.value, tasks_per_evaluation=u.value)
 
 
 _default_ctx = {}
@@ -300,6 +300,8 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     ret = {"results_dev": res_dev, "results": None}
     if sync:
         ret["results"] = res_dev[:B].cpu().numpy().view(RESULT_DTYPE).reshape(B)
+        if B and int(ret["results"]["status"].min()) < 0:
+            raise FmpnpError("fmpnp_refine_batch: the device scheduler gave up (FMPNP_STATUS_INCOMPLETE)")
         if track:
             ret["history"] = {k: v.cpu().numpy() for k, v in hbuf.items()}
     elif track:

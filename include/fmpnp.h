@@ -65,8 +65,10 @@ enum {
                                        (model.py:316-320, 441-445)                                          */
     FMPNP_STATUS_NAN_STEP = 2,      /* NaN in the step; loop left early, BEST pose returned (the intended
                                        behaviour of model.py:411-413)                                       */
-    FMPNP_STATUS_NO_INITIAL_COST = 3 /* multilevel only: compute_cost() was None, initial pose returned
+    FMPNP_STATUS_NO_INITIAL_COST = 3, /* multilevel only: compute_cost() was None, initial pose returned
                                        (model.py:183-187)                                                   */
+    FMPNP_STATUS_INCOMPLETE = -1    /* the kernel gave up before this query finished (scheduler watchdog):
+                                       the record is not a result                                           */
 };
 
 /* 6x6 solver for the damped step (replaces torch.lu + torch.lu_solve, model.py:51,61) */
@@ -104,9 +106,9 @@ typedef struct {
     int32_t n_levels;       /* 0: forward() on all channels; >0: multilevel_optimization */
     int32_t levels[FMPNP_MAX_LEVELS][2]; /* [start, end) channel slices, in execution order */
     int32_t solver;         /* FMPNP_SOLVER_* */
-    int32_t cluster_size;   /* CTAs (one thread-block cluster) refining each query together:
-                               0 = auto (1 when B fills the GPU, up to 16 for a single query),
-                               else 1, 2, 4, 8 or 16 */
+    int32_t cluster_size;   /* 0 = automatic: the task scheduler (an evaluation is cut into tasks that any CTA
+                               can run; every CTA stays busy for any batch size).  1, 2, 4, 8 or 16 = refine
+                               each query with one thread-block cluster of that many CTAs instead */
     int32_t reserved[6];
 } fmpnp_options;
 
@@ -207,8 +209,10 @@ int fmpnp_blur_chw(fmpnp_ctx *ctx, const void *src, int32_t src_is_f64, const do
 int64_t fmpnp_launch_count(const fmpnp_ctx *ctx);
 
 /* Launch geometry of the most recent kernel of this context: CTAs in the grid, CTAs per query
- * (thread-block cluster size) and bytes of shared-memory staging ring per CTA.  Diagnostics. */
-int fmpnp_last_geometry(const fmpnp_ctx *ctx, int32_t *grid, int32_t *cluster_size, int32_t *ring_bytes);
+ * (thread-block cluster size; 1 under the task scheduler), bytes of shared-memory staging ring per CTA and
+ * tasks per pose evaluation (0 = one CTA / cluster per query, no task queue).  Diagnostics. */
+int fmpnp_last_geometry(const fmpnp_ctx *ctx, int32_t *grid, int32_t *cluster_size, int32_t *ring_bytes,
+                        int32_t *tasks_per_evaluation);
 
 /* sizeof() of the ABI structs (0 problem, 1 options, 2 result, 3 history), so that a binding
  * in another language can verify its mirrors; -1 for an unknown index. */

@@ -1,5 +1,7 @@
 """GPU: shapes and exit paths beyond the golden fixtures, checked against the oracle, plus
 size-independent properties at the BASELINE.json sizes (N = 4096, C = 1024, 128 x 128 maps)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -125,19 +127,23 @@ def test_more_queries_than_resident_ctas():
                                       levels=[(512, 1024), (128, 512), (0, 128)]),
                                  dict(N=45, C=20, loss="huber_loss", ratio=None, levels=[(8, 20), (0, 8)])])
 def test_cluster_sizes_match_oracle_and_each_other(cfg):
-    """The result does not depend on how many CTAs share a query: the reduction order is fixed
-    (16 point ranges, pairwise tree), so records are bit-identical for cluster sizes 1..16."""
+    """The result does not depend on how many CTAs share a query, or on whether they are a cluster or
+    workers of the task scheduler: the reduction order is fixed (16 point ranges, pairwise tree), so
+    records are bit-identical for cluster sizes 1..16 and for the scheduler (cluster_size=0)."""
     sc = synth().make_scene(61, N=cfg["N"], C=cfg["C"], Hf=16, Wf=16, im_width=128, im_height=128,
                             K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
                             outlier_frac=0.1)
     p = to_problem(sc)
     o = run_oracle(sc, 6, cfg["loss"], 0.01, cfg["ratio"], cfg["levels"])
     first = None
-    for S in (1, 2, 4, 8, 16):
+    for S in (1, 2, 4, 8, 16, 0):
         out = fm().refine_batch([p], 6, loss=cfg["loss"], lambda_=0.01, ratio_threshold=cfg["ratio"],
                                 levels=cfg["levels"], track=True, cluster_size=S)
         g = fm().default_context().last_geometry
-        assert g["cluster_size"] == S and g["grid"] == S, g
+        if S:
+            assert g["cluster_size"] == S and g["grid"] == S and g["tasks_per_evaluation"] == 0, g
+        else:  # automatic: a single query goes to one cluster (16 CTAs, or 8 with the whole shared memory each)
+            assert g["cluster_size"] in (8, 16) and g["grid"] == g["cluster_size"] and g["tasks_per_evaluation"] == 0, g
         compare("cluster=%d" % S, out["results"][0], out["history"], o, use_ratio=cfg["ratio"] is not None)
         if first is None:
             first = out
@@ -145,11 +151,28 @@ def test_cluster_sizes_match_oracle_and_each_other(cfg):
             assert same_records(out["results"], first["results"]), "cluster=%d differs from cluster=1" % S
             for k in ("costs", "Rs", "ts", "points2d", "mask", "kept"):
                 assert np.array_equal(out["history"][k], first["history"][k], equal_nan=k in ("costs", "Rs", "ts")), k
+    # the task scheduler with 1..16 tasks per evaluation (FMPNP_UNITS is read when a context is created)
+    for U in (1, 2, 4, 8, 16):
+        os.environ["FMPNP_UNITS"] = str(U)
+        try:
+            ctx = fm().Context()
+        finally:
+            del os.environ["FMPNP_UNITS"]
+        out = fm().refine_batch([p, p, p], 6, loss=cfg["loss"], lambda_=0.01, ratio_threshold=cfg["ratio"],
+                                levels=cfg["levels"], track=True, ctx=ctx)
+        g = ctx.last_geometry
+        assert g["cluster_size"] == 1 and g["tasks_per_evaluation"] == U and g["grid"] == 3 * U, g
+        ctx.close()
+        for i in range(3):
+            assert same_records(out["results"][i], first["results"][0]), "units=%d differs from cluster=1" % U
+        for k in ("costs", "Rs", "ts", "points2d", "mask", "kept"):
+            assert np.array_equal(out["history"][k][0], first["history"][k][0], equal_nan=k in ("costs", "Rs", "ts")), k
+            assert np.array_equal(out["history"][k][2], first["history"][k][0], equal_nan=k in ("costs", "Rs", "ts")), k
 
 
 def test_automatic_geometry_and_batch_size_independence():
-    """Auto geometry: clusters for small batches, one CTA per query for large ones; the records of a
-    query are bit-identical whatever batch it is part of."""
+    """Auto geometry (task scheduler): many tasks per evaluation for small batches, one for large ones;
+    the records of a query are bit-identical whatever batch it is part of."""
     scs = [synth().make_scene(300 + i, N=500, C=1024, Hf=16, Wf=16, im_width=128, im_height=128,
                               K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
                               outlier_frac=0.1) for i in range(3)]
@@ -157,15 +180,19 @@ def test_automatic_geometry_and_batch_size_independence():
     ctx = fm().default_context()
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     ref = None
-    for B in (1, 3, 20, 70, sms, sms + 1, 2 * sms + 5):
+    for B in (1, 3, 20, 70, sms, sms + 1, 2 * sms + 5, 6 * sms + 1):
         batch = [probs[i % 3] for i in range(B)]
         r = fm().refine_batch(batch, 5, loss="geman_mcclure_loss", lambda_=0.01)["results"]
         g = ctx.last_geometry
-        assert g["grid"] % g["cluster_size"] == 0 and g["grid"] <= 2 * sms
-        if B > sms:
-            assert g["cluster_size"] == 1
+        U = g["tasks_per_evaluation"]
+        if B * 32 <= sms:  # a handful of queries: one cluster each
+            assert g["cluster_size"] in (8, 16) and U == 0 and g["grid"] == g["cluster_size"] * B, g
+        else:
+            assert g["cluster_size"] == 1 and U in (1, 2, 4, 8, 16) and g["grid"] <= min(2 * sms, B * U), g
+            assert U == 16 or B * U >= 6 * sms, g   # about three tasks per CTA slot, at most 16 per evaluation
+        if B >= 6 * sms:
+            assert U == 1
         if B == 1:
-            assert g["cluster_size"] >= 8
             ref = r
         for i in range(B):
             assert same_records(r[i], ref[0]) if i % 3 == 0 else True
