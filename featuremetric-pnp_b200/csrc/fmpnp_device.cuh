@@ -335,6 +335,11 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
 __device__ __forceinline__ void cp_async16_s(uint32_t smem_dst, const void* gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
 }
+// same, both addresses displaced by the compile-time OFF (one address computation serves a whole row)
+template <int OFF>
+__device__ __forceinline__ void cp_async16_off(uint32_t smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0+%2], [%1+%2], 16;" ::"r"(smem_dst), "l"(gmem_src), "n"(OFF) : "memory");
+}
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));

@@ -203,6 +203,42 @@ __device__ __forceinline__ double reduce_six(const double (&a)[6], int lane) {
     return v;
 }
 
+// The same halving butterfly over a group of L = 1 << LOG2L lanes (2 <= LOG2L <= 4) that share one point:
+// six values -> three -> two -> one, then plain butterfly steps.  Lane sl of the group ends up with the
+// totals number s0 (in v0) and, for groups of four lanes only, s1 (in v1); -1 = nothing to write.
+template <int LOG2L>
+__device__ __forceinline__ void reduce_group(const double (&a)[6], int sl, double& v0, double& v1, int& s0, int& s1) {
+    constexpr int D = 1 << (LOG2L - 1);
+    const bool hA = sl & D, hB = sl & (D >> 1);
+    double k0 = hA ? a[3] : a[0], k1 = hA ? a[4] : a[1], k2 = hA ? a[5] : a[2];
+    const double x0 = hA ? a[0] : a[3], x1 = hA ? a[1] : a[4], x2 = hA ? a[2] : a[5];
+    k0 = __dadd_rn(k0, shfl_xor_f64(x0, D));
+    k1 = __dadd_rn(k1, shfl_xor_f64(x1, D));
+    k2 = __dadd_rn(k2, shfl_xor_f64(x2, D));
+    double m0 = hB ? k2 : k0, m1 = hB ? 0.0 : k1;
+    const double t0 = hB ? k0 : k2, t1 = hB ? k1 : 0.0;
+    m0 = __dadd_rn(m0, shfl_xor_f64(t0, D >> 1));
+    m1 = __dadd_rn(m1, shfl_xor_f64(t1, D >> 1));
+    const int base = hA ? 3 : 0;
+    if (LOG2L == 2) {
+        v0 = m0;
+        v1 = m1;
+        s0 = base + (hB ? 2 : 0);
+        s1 = hB ? -1 : base + 1;
+        return;
+    }
+    const bool hC = sl & (D >> 2);
+    double v = hC ? m1 : m0;
+    const double u = hC ? m0 : m1;
+    v = __dadd_rn(v, shfl_xor_f64(u, D >> 2));
+#pragma unroll
+    for (int d = D >> 3; d > 0; d >>= 1) v = __dadd_rn(v, shfl_xor_f64(v, d));
+    v0 = v;
+    v1 = 0.0;
+    s1 = -1;
+    s0 = ((sl & ((D >> 2) - 1)) || (hB && hC)) ? -1 : base + (hB ? 2 : (hC ? 1 : 0));
+}
+
 // lane -> slot of the 6-double record it writes after reduce_six (or -1)
 __device__ __forceinline__ int six_slot(int lane) {
     if (lane & 3) return -1;
@@ -235,6 +271,24 @@ __device__ __forceinline__ void acc4(uint32_t aF, uint32_t aGx, uint32_t aGy, ui
     acc1<GRAD>(f.y, r.y, gx.y, gy.y, a);
     acc1<GRAD>(f.z, r.z, gx.z, gy.z, a);
     acc1<GRAD>(f.w, r.w, gx.w, gy.w, a);
+}
+
+// FULL whole-warp copies (512 B each) of each of the ROWS rows s[r] to dst + r * rowB
+template <int ROWS, int FULL>
+__device__ __forceinline__ void copy_rows_full(uint32_t dst, const char* const (&s)[4], uint32_t rowB) {
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+        const uint32_t d = dst + (uint32_t)r * rowB;
+        const char* g = s[r];
+        if (FULL > 0) cp_async16_off<0>(d, g);
+        if (FULL > 1) cp_async16_off<512>(d, g);
+        if (FULL > 2) cp_async16_off<1024>(d, g);
+        if (FULL > 3) cp_async16_off<1536>(d, g);
+        if (FULL > 4) cp_async16_off<2048>(d, g);
+        if (FULL > 5) cp_async16_off<2560>(d, g);
+        if (FULL > 6) cp_async16_off<3072>(d, g);
+        if (FULL > 7) cp_async16_off<3584>(d, g);
+    }
 }
 
 template <bool GRAD, int LOG2L>
@@ -291,17 +345,34 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
         }
         dst += lane * 16;
         const int full = nv >> 5, tail = nv & 31;  // whole 512-byte warp copies, then a partial one
+        if (SHORT) {  // nv <= 32: one 16-byte piece of every row per lane
+            if (lane < nv) {
+#pragma unroll
+                for (int r = 0; r < ROWS; ++r) cp_async16_s(dst + (uint32_t)(r * nv) * 16u, s[r]);
+            }
+            return;
+        }
+        if (tail == 0 && full <= 8) {  // the usual case: immediate offsets, no loop
+            const uint32_t rowB = (uint32_t)nv * 16u;
+            switch (full) {
+                case 1: copy_rows_full<ROWS, 1>(dst, s, rowB); break;
+                case 2: copy_rows_full<ROWS, 2>(dst, s, rowB); break;
+                case 3: copy_rows_full<ROWS, 3>(dst, s, rowB); break;
+                case 4: copy_rows_full<ROWS, 4>(dst, s, rowB); break;
+                case 5: copy_rows_full<ROWS, 5>(dst, s, rowB); break;
+                case 6: copy_rows_full<ROWS, 6>(dst, s, rowB); break;
+                case 7: copy_rows_full<ROWS, 7>(dst, s, rowB); break;
+                default: copy_rows_full<ROWS, 8>(dst, s, rowB); break;
+            }
+            return;
+        }
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
             uint32_t d = dst + (uint32_t)(r * nv) * 16u;
             const char* g = s[r];
-            if (SHORT) {  // nv <= 32
-                if (lane < nv) cp_async16_s(d, g);
-            } else {
 #pragma unroll 4
-                for (int i = 0; i < full; ++i, d += 512, g += 512) cp_async16_s(d, g);
-                if (lane < tail) cp_async16_s(d, g);
-            }
+            for (int i = 0; i < full; ++i, d += 512, g += 512) cp_async16_s(d, g);
+            if (lane < tail) cp_async16_s(d, g);
         }
     };
 
@@ -341,8 +412,18 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
                 const uint32_t p2 = p + L * 16;
                 acc4<GRAD>(p2, p2 + rowB, p2 + 2 * rowB, p2 + (ROWS - 1) * rowB, a);
             }
-            reduce_lanes<GRAD, LOG2L>(a);
-            if (act && sl == 0) write_record<GRAD>(a, c.rec + (size_t)bn[buf * 32 + k] * kRecDoubles);
+            double* rec_n = c.rec + (size_t)bn[buf * 32 + (act ? k : 0)] * kRecDoubles;
+            if (GRAD) {
+                constexpr int LG = SHORT ? LOG2L : 4;  // (the long-row instantiation never gets here)
+                double v0, v1;
+                int s0, s1;
+                reduce_group<LG>(a, sl, v0, v1, s0, s1);
+                if (act && s0 >= 0) rec_n[s0] = v0;
+                if (LG == 2 && act && s1 >= 0) rec_n[s1] = v1;
+            } else {
+                reduce_lanes<GRAD, LOG2L>(a);
+                if (act && sl == 0) rec_n[0] = a[0];
+            }
         } else {
             if (cch == 0) {
 #pragma unroll
