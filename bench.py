@@ -148,18 +148,29 @@ def scene_to_reference_problem(sc):
                 im_width=sc.im_width, im_height=sc.im_height), inp["R_init"].numpy(), inp["t_init"].numpy()
 
 
-def cpu_sample(args, cfg, n_queries, threads, scenes=None):
-    """Times `n_queries` full-shape queries with `threads` host threads; returns (queries/s, seconds).
-    `scenes`: reuse the (device-resident) scenes the GPU arm just processed."""
+def host_threads():
+    """Host threads the CPU arm uses: every core this process may run on, capped at 64 (each thread holds one
+    full-shape query in the reference's layout: ~0.45 GB of float64 CHW maps)."""
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    return max(1, min(cores, 64))
+
+
+def cpu_problems(args, cfg, n_queries, scenes=None):
+    """`n_queries` full-shape queries in the reference's layout (float64, CHW), inlier mask applied like cfg2 does.
+    Inputs are synthesised on the GPU when there is one (input generation only), else on the host."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle
     from fmpnp_b200 import synth
+    gen_dev = "cuda" if torch.cuda.is_available() else "cpu"
     probs, R0s, t0s = [], [], []
     for q in range(n_queries):
         if scenes is not None:
             sc = scenes[q]
         else:
-            sc = synth.make_scene(q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device="cpu")
+            sc = synth.make_scene(q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device=gen_dev)
         p, R0, t0 = scene_to_reference_problem(sc)
         if cfg["inlier_mask"]:
             inl = oracle.find_inliers(p["pts3D"], R0, t0, p["F"], p["feature_ref"], p["K"], p["im_width"], p["im_height"],
@@ -170,28 +181,42 @@ def cpu_sample(args, cfg, n_queries, threads, scenes=None):
         R0s.append(R0)
         t0s.append(t0)
         del sc
+    return probs, np.stack(R0s), np.stack(t0s)
+
+
+def cpu_pass(cfg, problems, threads):
+    """One timed pass of the CPU implementation over `problems`; returns seconds."""
+    import oracle
+    probs, R0s, t0s = problems
     t = time.perf_counter()
-    oracle.forward_batch(probs, np.stack(R0s), np.stack(t0s), cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+    oracle.forward_batch(probs, R0s, t0s, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
                          ratio_threshold=cfg["ratio_threshold"], levels=cfg["levels"], n_threads=threads)
-    dt = time.perf_counter() - t
+    return time.perf_counter() - t
+
+
+def cpu_sample(args, cfg, n_queries, threads, scenes=None):
+    """Times `n_queries` full-shape queries with `threads` host threads; returns (queries/s, seconds).
+    `scenes`: reuse the (device-resident) scenes the GPU arm just processed."""
+    problems = cpu_problems(args, cfg, n_queries, scenes)
+    dt = cpu_pass(cfg, problems, threads)
     return n_queries / dt, dt
 
 
 def run_reference(args, cfg, rank):
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
-    threads = max(1, min(cores, 16))
+    threads = host_threads()
     per_step = threads  # one full-shape query per thread per step
-    for _ in range(args.warmup if args.warmup < 1 else 1):  # one warm-up pass is enough on the CPU
-        cpu_sample(args, cfg, min(per_step, 2), min(threads, 2))
+    problems = cpu_problems(args, cfg, per_step)
+    if args.warmup > 0:  # one warm-up pass is enough on the CPU
+        cpu_pass(cfg, (problems[0][:2], problems[1][:2], problems[2][:2]), min(threads, 2))
     tot_q, tot_t = 0, 0.0
     for _ in range(max(1, args.steps)):
-        qps, dt = cpu_sample(args, cfg, per_step, threads)
+        tot_t += cpu_pass(cfg, problems, threads)
         tot_q += per_step
-        tot_t += dt
     v = tot_q / tot_t
-    sample = "%d full-shape queries per step, one per thread, %d step(s)" % (per_step, max(1, args.steps))
+    sample = "%d full-shape queries per step (seeds 0..%d of the same workload), one per thread, %d step(s)" % (
+        per_step, per_step - 1, max(1, args.steps))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
@@ -318,6 +343,7 @@ def main():
                 "algorithmic_bytes_per_launch": alg_bytes,
                 "nominal_bytes_per_launch": float(nominal) if levels is None else None,
                 "share_of_step": k_ms * args.steps / total_ms, "geometry": geo,
+                "kernel_ms_all": [round(x, 3) for x in kern_ms],
                 "peak_note": "peak is the measured COPY bandwidth (half reads, half writes); this kernel only reads, "
                              "so frac can exceed 1 - see dram__cycles_active in profiles/ for the remaining headroom"}
 
@@ -329,6 +355,8 @@ def main():
             "mean_evaluations_per_query": float(res["n_evaluations"].mean())}
 
     # ---- e2e: same C ABI, inputs start in pinned HOST memory, results end in host memory
+    near = sharding.host_near_gpu(local_rank)
+    near.__enter__()  # pinned buffers on the GPU's NUMA node (matters when several ranks copy at once)
     if not args.no_e2e:
         E = min(args.e2e_queries, B)
         names = ("F", "Gx", "Gy", "ref", "pts3D")
@@ -428,13 +456,16 @@ def main():
                                            "-> D2H; rank-local, not aggregated"}
             del qh_host, qh_dev, rh_dev
 
+    near.__exit__(None, None, None)
+    if "e2e" in line:
+        line["e2e"]["host_cores_near_gpu"] = near.cores
+
     # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle port on a bounded sample
     if rank == 0 and world == 1 and not args.no_cpu:
-        cores = os.cpu_count() or 1
-        threads = max(1, min(cores, 16))
+        threads = host_threads()
         nq = args.cpu_queries or threads
         try:
-            v, dt = cpu_sample(args, cfg, nq, threads, scenes=scenes)
+            v, dt = cpu_sample(args, cfg, nq, threads, scenes=scenes if nq <= len(scenes) else None)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "%d full-shape queries (seeds 0..%d of the same workload), one per thread, "
                                               "%.1f s wall" % (nq, nq - 1, dt)}

@@ -1,21 +1,25 @@
-// fmpnp_kernels.cu -- the feature-metric PnP refinement as ONE persistent sm_100a kernel.
+// fmpnp_kernels.cu -- the feature-metric PnP refinement as ONE persistent sm_100a kernel per batch.
 //
 // Replaces sparseFeaturePnP.forward / multilevel_optimization / compute_cost and find_inliers
-// of featurePnP/model.py (reference lines cited inline).  A CTA (or a thread-block cluster of up
-// to 16 CTAs when the batch is small) owns one query at a time and runs its whole
-// Levenberg-Marquardt loop on the device: no host synchronisation, no per-iteration launch,
-// no collective.
+// of featurePnP/model.py (reference lines cited inline).  The whole Levenberg-Marquardt loop of
+// every query runs on the device: no host synchronisation, no per-iteration launch, no
+// collective.  Queries reach CTAs in one of two ways (same device code below them):
+//   task scheduler   (*_tasks_kernel, default) a pose evaluation is cut into tasks on a global
+//                    FIFO; any CTA runs any task; the CTA that completes an evaluation advances
+//                    the query's LM state (kept in global memory) and queues the next evaluation;
+//   CTA / cluster    (*_kernel) a CTA, or a thread-block cluster of up to 16 CTAs exchanging
+//                    partial sums through distributed shared memory, owns one query at a time.
 //
 // Per pose evaluation (the only part that touches HBM in bulk):
 //   every warp      projects 32 points at a time in float64 (bit-exact pixel indices), then
 //                   streams their channel-contiguous rows F[cell], Gx[cell], Gy[cell], ref[n]
-//                   through its own slice of a shared-memory ring: TMA bulk copies
-//                   (cp.async.bulk -> SASS UBLKCP) signalled on mbarriers, several items in
-//                   flight per warp, the next batch projected while the last rows of the
-//                   current one are still landing.  The staged rows are read as float4 and
-//                   accumulated in float64 into the per-point c = sum e^2, the 2x2 structure
-//                   tensor S = G^T G and b = G^T e; short rows share a warp (L lanes per point),
-//                   long rows are cut into channel chunks.  One 48-byte record per point;
+//                   through its own slice of a shared-memory ring with cp.async (SASS
+//                   LDGSTS.E.BYPASS.128, one commit group per item, several items in flight),
+//                   the next batch projected while the last rows of the current one are still
+//                   landing.  The staged rows are read as float4 and accumulated in float64
+//                   into the per-point c = sum e^2, the 2x2 structure tensor S = G^T G and
+//                   b = G^T e; short rows share a warp (L lanes per point), long rows are cut
+//                   into channel chunks.  One 48-byte record per point;
 //   all threads     apply the robust loss / ratio test, contract (S, b) with the 2x6
 //                   projection Jacobian and reduce the 6x6 normal equations in a fixed order
 //                   (16 point ranges, pairwise tree: the same bits for any launch geometry);
@@ -25,7 +29,7 @@
 // step is accepted, so every LM iteration gathers each map exactly once: 4*N*C*4 bytes.
 //
 // Channel ranges that are not 16-byte aligned (C, slice start or slice length not a multiple
-// of 4) take a generic path with direct coalesced global loads instead of TMA.
+// of 4) take a generic path with direct coalesced global loads instead of the staged one.
 #include <cmath>
 #include <cstdint>
 
@@ -62,19 +66,17 @@ struct __align__(16) Shared {
     int32_t bl_n[kWarps][2][32];
 };
 
-// Position inside a warp's slice of the ring.  Bit i of `bits` is the phase parity of the next
-// use of slot i's barrier.  The ring is empty between evaluations, so an evaluation with a
-// different depth simply starts again at slot 0 and keeps the per-slot parities.
+// Position inside a warp's slice of the ring.  The ring is empty between evaluations, so an evaluation
+// with a different depth simply starts again at slot 0.
 struct RingPos {
-    int32_t pos;    // next slot to consume
-    uint32_t bits;  // per-slot mbarrier phase parity
-    int32_t cpar;   // which half of Shared::cpart the next cluster reduction uses
+    int32_t pos;   // next slot to consume
+    int32_t cpar;  // which half of Shared::cpart the next cluster reduction uses
 };
 
 struct EvalCtx {
     const QueryDev* q;
     int32_t c0, Cl;        // channel slice [c0, c0 + Cl)
-    bool aligned;          // TMA path allowed
+    bool aligned;          // staged (16-byte) path allowed
     int32_t loss_id;
     double alpha;
     int32_t ratio_mode;    // 0 none, 1 on rho (forward / find_inliers), 2 on raw SSD (compute_cost)
@@ -864,7 +866,6 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     if (csize > 1) cg::this_cluster().sync();  // every CTA of the cluster is resident before any remote access
     RingPos rp;
     rp.pos = 0;
-    rp.bits = 0;
     rp.cpar = 0;
     double* rec = p.rec + (size_t)blockIdx.x * p.n_max * kRecDoubles;
     uint8_t* supp = p.supp + (size_t)blockIdx.x * p.n_max;
@@ -1272,7 +1273,6 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
     const SchedDev& sc = p.sched;
     RingPos rp;
     rp.pos = 0;
-    rp.bits = 0;
     rp.cpar = 0;
 
     // ---- every CTA starts a share of the queries: initial state + the tasks of their first evaluation

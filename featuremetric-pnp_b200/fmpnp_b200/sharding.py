@@ -43,3 +43,42 @@ def gather_result_records(local_records, n_queries, group=None):
 
 def records_to_numpy(records, dtype):
     return np.ascontiguousarray(records.cpu().numpy()).view(dtype).reshape(-1)
+
+
+class host_near_gpu:
+    """Context manager: runs the calling process on the CPU cores next to `device` (NVML's ideal affinity), so
+    that pinned host buffers allocated inside are on the GPU's NUMA node and H2D copies of several ranks do not
+    cross the socket interconnect.  Restores the previous affinity on exit; does nothing when NVML or the
+    affinity calls are unavailable."""
+
+    def __init__(self, device_index):
+        self.device_index, self.saved, self.cores = device_index, None, None
+
+    def __enter__(self):
+        try:
+            import os
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = torch.cuda.get_device_properties(self.device_index).uuid
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+            n_words = (os.cpu_count() + 63) // 64
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+            cores = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+            allowed = os.sched_getaffinity(0)
+            cores &= allowed
+            if cores:
+                self.saved = allowed
+                os.sched_setaffinity(0, cores)
+                self.cores = len(cores)
+        except Exception:
+            self.saved = None
+        return self
+
+    def __exit__(self, *a):
+        if self.saved is not None:
+            import os
+            try:
+                os.sched_setaffinity(0, self.saved)
+            except Exception:
+                pass
+        return False
