@@ -79,7 +79,7 @@ def compare(name, res, hist, o, b=0, use_ratio=False, sel=None):
 # ----------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("C,levels", [(1024, None), (640, None), (1024, [(512, 1024), (128, 512), (0, 128)]),
                                       (2048, [(1024, 2048), (256, 1024), (0, 256)]), (516, None), (20, [(8, 20), (0, 8)])])
-def test_wide_and_chunked_channels(C, levels):
+def test_wide_and_chunked_channels(C, levels, route):
     sc = synth().make_scene(21, N=200, C=C, Hf=16, Wf=16, im_width=128, im_height=128,
                             K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
                             outlier_frac=0.1)
@@ -91,7 +91,7 @@ def test_wide_and_chunked_channels(C, levels):
 # ----------------------------------------------------------------------------------------------
 # a ragged batch: different N per query, one launch
 # ----------------------------------------------------------------------------------------------
-def test_ragged_batch_matches_oracle_and_single_runs():
+def test_ragged_batch_matches_oracle_and_single_runs(route):
     Ns = [1, 7, 33, 150, 257, 64, 300, 96, 5, 211]
     scs = [synth().make_scene(40 + i, N=n, C=32, grad_scale=1.0 / 64, outlier_frac=0.1, **SMALL) for i, n in enumerate(Ns)]
     probs = [to_problem(sc) for sc in scs]
@@ -209,7 +209,7 @@ def test_automatic_geometry_and_batch_size_independence():
 # ----------------------------------------------------------------------------------------------
 # exit paths
 # ----------------------------------------------------------------------------------------------
-def test_no_supported_point_returns_initial_pose():
+def test_no_supported_point_returns_initial_pose(route):
     sc = synth().make_scene(50, N=30, C=8, **SMALL)
     t_far = sc.t0.clone()
     t_far[0] += 1000.0  # everything projects outside the image
@@ -228,7 +228,7 @@ def test_no_supported_point_returns_initial_pose():
     assert int(ns[0]) == 0 and torch.isnan(c[0])
 
 
-def test_zero_points():
+def test_zero_points(route):
     sc = synth().make_scene(51, N=4, C=8, **SMALL)
     sc.pts3D = sc.pts3D[:0].contiguous()
     sc.ref = sc.ref[:0].contiguous()
@@ -237,7 +237,7 @@ def test_zero_points():
     assert fm().find_inliers_batch([to_problem(sc)], 0.8).shape[0] == 1
 
 
-def test_nan_step_breaks_and_returns_best():
+def test_nan_step_breaks_and_returns_best(route):
     """Gauss-Newton (lambda_ = 0) with identically zero gradient maps: H = 0, g = 0, LU meets a
     zero pivot, the step is 0/0 = NaN, the loop is left and the best (= initial) pose returned
     (the intent of model.py:411-413)."""
@@ -256,7 +256,7 @@ def test_nan_step_breaks_and_returns_best():
     compare("zero-gradient damped", out["results"][0], out["history"], o2)
 
 
-def test_ratio_test_that_removes_every_point():
+def test_ratio_test_that_removes_every_point(route):
     """One supported point: |rho| < thr * max|rho| is false for it -> zero survivors, cost = nan,
     H = g = 0; the reference then keeps 'accepting' nan costs. Must match the oracle exactly."""
     sc = synth().make_scene(53, N=1, C=8, **SMALL)
@@ -266,7 +266,7 @@ def test_ratio_test_that_removes_every_point():
     assert np.isnan(out["history"]["costs"][0, 0]) and int(out["results"][0]["best_num_inliers"]) == 0
 
 
-def test_step_that_leaves_the_image_returns_current_pose():
+def test_step_that_leaves_the_image_returns_current_pose(route):
     """Tiny gradients -> tiny H -> huge undamped step -> no supported point at the trial pose:
     forward returns the CURRENT pose (model.py:441-445)."""
     sc = synth().make_scene(54, N=60, C=8, grad_scale=1e-9, **SMALL)
@@ -275,7 +275,7 @@ def test_step_that_leaves_the_image_returns_current_pose():
     compare("fly-away", out["results"][0], out["history"], o)
 
 
-def test_points_behind_the_camera_are_not_filtered():
+def test_points_behind_the_camera_are_not_filtered(route):
     sc = synth().make_scene(55, N=80, C=8, grad_scale=1.0 / 64, **SMALL)
     pts = sc.pts3D.clone()
     pts[::3] *= -1.0  # mirrored through the camera centre: same pixel, negative depth
@@ -286,7 +286,7 @@ def test_points_behind_the_camera_are_not_filtered():
     assert o["track"]["mask"][0][::3].any()
 
 
-def test_active_mask_equals_compaction():
+def test_active_mask_equals_compaction(route):
     """fmpnp_problem.active == passing pts3D[inliers], feature_ref[inliers] (optimize_feature_pnp.py:43-44)."""
     sc = synth().make_scene(56, N=150, C=16, grad_scale=1.0 / 64, outlier_frac=0.2, **SMALL)
     inl = fm().find_inliers_batch([to_problem(sc)], 0.8, loss="squared_loss")[0].cpu().numpy().astype(bool)
@@ -301,7 +301,7 @@ def test_active_mask_equals_compaction():
     compare("active-mask", out["results"][0], out["history"], o, use_ratio=True, sel=sel)
 
 
-def test_unaligned_views_take_the_generic_path():
+def test_unaligned_views_take_the_generic_path(route):
     """Descriptor / map tensors whose base address is not 16-byte aligned (a slice of a larger buffer)."""
     sc = synth().make_scene(57, N=64, C=16, grad_scale=1.0 / 64, **SMALL)
     dev = "cuda"

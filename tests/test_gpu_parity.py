@@ -48,9 +48,10 @@ def check_against(name, res, hist, exp, use_ratio, b=0):
     assert abs(float(res["best_cost"]) - exp["best_cost"]) <= TIGHT * abs(exp["best_cost"]), name
 
 
-@pytest.mark.parametrize("solver", ["cholesky", "lu"])
+@pytest.mark.parametrize("solver,route", [("cholesky", "auto"), ("lu", "auto"), ("cholesky", "tasks2"),
+                                          ("cholesky", "tasks16")], indirect=["route"])
 @pytest.mark.parametrize("name", golden_names())
-def test_c_abi_matches_reference_fixture(name, solver):
+def test_c_abi_matches_reference_fixture(name, solver, route):
     fm = _fm()
     g = load_golden(name)
     prob = problem_from_golden(g)
