@@ -404,7 +404,8 @@ def main():
                        "d2h_bytes_per_step": int(d2h), "queries_per_step": E, "steps": ksteps,
                        "h2d_gbs": h2d * ksteps / (e_ms / 1e3) / 1e9,
                        "note": "HWC fp32 maps + descriptors + points in pinned host memory -> H2D -> find_inliers + "
-                               "refine kernels -> result records D2H, all inside the timed region (PCIe-bound)"}
+                               "refine kernels -> result records D2H, all inside the timed region (PCIe-bound; cutting the step into "
+                               "chunks whose uploads overlap the kernels measured 5 % slower and was dropped)"}
         del host, devbuf
 
         # ---- e2e one level up (the reference's feature_pnp): hypercolumns in pinned host memory -> H2D ->
@@ -456,6 +457,34 @@ def main():
                                            "-> D2H; rank-local, not aggregated"}
             del qh_host, qh_dev, rh_dev
 
+    # ---- e2e at the reference's own Python call: sparseFeaturePnP.forward, one query per call, CPU float64 CHW
+    # tensors in (what s2dhm hands over today), CPU float64 pose out.  Rank-local, cfg3/cfg2 losses only.
+    if not args.no_e2e and levels is None:
+        import model as dropin
+        from helpers import utils as hu
+        D = min(4, B)
+        ins = [scenes[i].reference_inputs() for i in range(D)]
+        m = dropin.sparseFeaturePnP(n_iters=cfg["n_iters"], loss_fn=getattr(hu, cfg["loss"]), lambda_=cfg["lambda_"],
+                                    ratio_threshold=cfg["ratio_threshold"])
+
+        def dropin_query(x):
+            dropin.clear_pack_cache()
+            return m(x["pts3D"], x["feature_ref"], x["feature_map_query"], x["feature_grad_x"], x["feature_grad_y"],
+                     x["K"], x["im_width"], x["im_height"], R_init=x["R_init"], t_init=x["t_init"])
+
+        dropin_query(ins[0])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for x in ins:
+            dropin_query(x)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        per_q = sum(x[k].numel() * x[k].element_size() for x in ins[:1]
+                    for k in ("pts3D", "feature_ref", "feature_map_query", "feature_grad_x", "feature_grad_y"))
+        line["e2e_dropin"] = {"value": D / dt, "unit": UNIT + " per GPU", "h2d_bytes_per_query": int(per_q), "queries": D,
+                              "note": "model.sparseFeaturePnP.forward per query: pageable CPU float64 CHW tensors -> H2D -> "
+                                      "pack kernel -> refinement -> CPU float64 pose; wall clock, no inlier mask"}
+        del ins
     near.__exit__(None, None, None)
     if "e2e" in line:
         line["e2e"]["host_cores_near_gpu"] = near.cores

@@ -22,10 +22,11 @@ struct fmpnp_ctx {
     char err[512] = {0};
     // device copy of the problem descriptors + pinned staging
     QueryDev* d_queries = nullptr;
-    QueryDev* h_queries = nullptr;
+    QueryDev* h_queries[2] = {nullptr, nullptr};  // pinned staging, alternating between consecutive calls
     size_t cap_queries = 0;
-    cudaEvent_t staged = nullptr;
-    bool staged_pending = false;
+    cudaEvent_t staged[2] = {nullptr, nullptr};
+    bool staged_pending[2] = {false, false};
+    int stage_slot = 0;
     // per-CTA scratch
     double* d_rec = nullptr;
     uint8_t* d_supp = nullptr;
@@ -92,29 +93,35 @@ int validate_problem(fmpnp_ctx* ctx, const fmpnp_problem& p, int b, bool need_gr
 // copies the descriptors to the device (through pinned staging) and sizes the per-CTA scratch
 int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32_t* n_max_out, cudaStream_t stream) {
     if ((size_t)B > ctx->cap_queries) {
-        if (ctx->staged_pending) {
-            FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged));
-            ctx->staged_pending = false;
+        for (int i = 0; i < 2; ++i) {
+            if (ctx->staged_pending[i]) {
+                FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged[i]));
+                ctx->staged_pending[i] = false;
+            }
         }
         size_t cap = ctx->cap_queries ? ctx->cap_queries : 256;
         while (cap < (size_t)B) cap *= 2;
         if (ctx->d_queries) FMPNP_CUDA(ctx, cudaFree(ctx->d_queries));
-        if (ctx->h_queries) FMPNP_CUDA(ctx, cudaFreeHost(ctx->h_queries));
         ctx->d_queries = nullptr;
-        ctx->h_queries = nullptr;
         ctx->cap_queries = 0;
+        for (int i = 0; i < 2; ++i) {
+            if (ctx->h_queries[i]) FMPNP_CUDA(ctx, cudaFreeHost(ctx->h_queries[i]));
+            ctx->h_queries[i] = nullptr;
+        }
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_queries, cap * sizeof(QueryDev)));
-        FMPNP_CUDA(ctx, cudaMallocHost(&ctx->h_queries, cap * sizeof(QueryDev)));
+        for (int i = 0; i < 2; ++i) FMPNP_CUDA(ctx, cudaMallocHost(&ctx->h_queries[i], cap * sizeof(QueryDev)));
         ctx->cap_queries = cap;
     }
-    if (ctx->staged_pending) {  // previous call's H2D copy must have left the staging buffer
-        FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged));
-        ctx->staged_pending = false;
+    const int slot = ctx->stage_slot;
+    ctx->stage_slot ^= 1;
+    if (ctx->staged_pending[slot]) {  // the H2D copy of the call before the previous one must have left this buffer
+        FMPNP_CUDA(ctx, cudaEventSynchronize(ctx->staged[slot]));
+        ctx->staged_pending[slot] = false;
     }
     int32_t n_max = 1;
     for (int32_t b = 0; b < B; ++b) {
         const fmpnp_problem& p = probs[b];
-        QueryDev& q = ctx->h_queries[b];
+        QueryDev& q = ctx->h_queries[slot][b];
         q.F = p.F;
         q.Gx = p.Gx;
         q.Gy = p.Gy;
@@ -132,10 +139,10 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
         q.im_h = p.im_height;
         if (p.N > n_max) n_max = p.N;
     }
-    FMPNP_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries, ctx->h_queries, (size_t)B * sizeof(QueryDev), cudaMemcpyHostToDevice,
-                                    stream));
-    FMPNP_CUDA(ctx, cudaEventRecord(ctx->staged, stream));
-    ctx->staged_pending = true;
+    FMPNP_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries, ctx->h_queries[slot], (size_t)B * sizeof(QueryDev),
+                                    cudaMemcpyHostToDevice, stream));
+    FMPNP_CUDA(ctx, cudaEventRecord(ctx->staged[slot], stream));
+    ctx->staged_pending[slot] = true;
     const size_t need = (size_t)grid * (size_t)n_max;
     if (need > ctx->cap_points) {
         if (ctx->d_rec) FMPNP_CUDA(ctx, cudaFree(ctx->d_rec));
@@ -152,13 +159,14 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
 }
 
 // Launch geometry.
-//   * Batches that fill the GPU (B > 148): one CTA per query, 2 CTAs per SM, a 96 KB staging ring each
-//     (measured 0.95 of the HBM copy peak at B = 256).
-//   * Smaller batches: a thread-block cluster of 2..16 CTAs refines each query together (the points are
-//     split, the normal equations combined through distributed shared memory), so that all SMs stream
-//     even for a single query; when that still leaves at most one CTA per SM each CTA takes the whole
-//     shared memory as its ring.
-// FMPNP_RING_KB / FMPNP_MIN_DEPTH / FMPNP_CTAS_PER_SM / FMPNP_CLUSTER override the choice (tuning only).
+//   * Default: the task scheduler.  An evaluation is cut into U tasks (1..16) so that about three tasks per
+//     CTA slot exist; 2 CTAs per SM with a 96 KB staging ring each, or one CTA per SM with the whole shared
+//     memory when there is at most one task per SM.
+//   * A handful of queries (B <= 4), an explicit cluster_size or FMPNP_SCHEDULER=0: one CTA, or a
+//     thread-block cluster of 2..16 CTAs, per query (the points are split, the normal equations combined
+//     through distributed shared memory).
+// FMPNP_RING_KB / FMPNP_MIN_DEPTH / FMPNP_CTAS_PER_SM / FMPNP_CLUSTER / FMPNP_UNITS override the choice
+// (tuning and tests only).
 struct Geometry {
     int grid, ring_bytes, ring_per_warp, min_depth, cluster, units;
 };
@@ -318,7 +326,8 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
         cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
         cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess ||
         cudaMalloc(&ctx->d_counter, sizeof(unsigned int)) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->staged, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&ctx->staged[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->staged[1], cudaEventDisableTiming) != cudaSuccess) {
         delete ctx;
         return FMPNP_ERR_CUDA;
     }
@@ -335,9 +344,10 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
 int fmpnp_destroy(fmpnp_ctx* ctx) {
     if (!ctx) return FMPNP_SUCCESS;
     cudaSetDevice(ctx->device);
-    if (ctx->staged_pending) cudaEventSynchronize(ctx->staged);
+    cudaDeviceSynchronize();
     if (ctx->d_queries) cudaFree(ctx->d_queries);
-    if (ctx->h_queries) cudaFreeHost(ctx->h_queries);
+    for (int i = 0; i < 2; ++i)
+        if (ctx->h_queries[i]) cudaFreeHost(ctx->h_queries[i]);
     if (ctx->d_rec) cudaFree(ctx->d_rec);
     if (ctx->d_supp) cudaFree(ctx->d_supp);
     if (ctx->d_counter) cudaFree(ctx->d_counter);
@@ -345,7 +355,8 @@ int fmpnp_destroy(fmpnp_ctx* ctx) {
     if (ctx->d_part) cudaFree(ctx->d_part);
     if (ctx->d_queue) cudaFree(ctx->d_queue);
     if (ctx->d_sched) cudaFree(ctx->d_sched);
-    if (ctx->staged) cudaEventDestroy(ctx->staged);
+    for (int i = 0; i < 2; ++i)
+        if (ctx->staged[i]) cudaEventDestroy(ctx->staged[i]);
     delete ctx;
     return FMPNP_SUCCESS;
 }
