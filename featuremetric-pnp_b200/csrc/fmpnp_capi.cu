@@ -282,14 +282,15 @@ int prepare_tasks(fmpnp_ctx* ctx, int32_t B, const Geometry& g, LaunchParams& lp
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_queue, (size_t)cap * sizeof(unsigned long long)));
         ctx->cap_queue = cap;
     }
-    if (!ctx->d_sched) FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_sched, 4 * sizeof(unsigned int)));
+    if (!ctx->d_sched) FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_sched, 8 * sizeof(unsigned int)));
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0xff, (size_t)ctx->cap_queue * sizeof(unsigned long long), stream));
-    FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_sched, 0, 4 * sizeof(unsigned int), stream));
+    FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_sched, 0, 8 * sizeof(unsigned int), stream));
     lp.sched.queue = ctx->d_queue;
     lp.sched.head = ctx->d_sched;
     lp.sched.tail = ctx->d_sched + 1;
     lp.sched.done = ctx->d_sched + 2;
     lp.sched.error = ctx->d_sched + 3;
+    lp.sched.started = ctx->d_sched + 4;
     lp.sched.cap = ctx->cap_queue;
     lp.sched.units = g.units;
     lp.sched.states = ctx->d_states;

@@ -1275,45 +1275,51 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
     rp.pos = 0;
     rp.cpar = 0;
 
-    // ---- every CTA starts a share of the queries: initial state + the tasks of their first evaluation
-    if (tid == 0) {
-        for (int q = blockIdx.x; q < p.B; q += gridDim.x) {
-            const QueryDev& qd = p.queries[q];
-            QueryState& g = sc.states[q];
-            for (int i = 0; i < 9; ++i) g.R[i] = g.Rn[i] = g.Rb[i] = qd.R0[i];
-            for (int i = 0; i < 3; ++i) g.t[i] = g.tn[i] = g.tb[i] = qd.t0[i];
-            for (int i = 0; i < 27; ++i) g.lin[i] = 0.0;
-            g.prev_cost = g.best_cost = NAN;
-            g.lambda = p.lambda0;
-            g.lr = 1.0;
-            g.initial_cost = NAN;
-            g.gathered = 0;
-            g.best_n = -1;
-            g.has_best = 0;
-            g.status = FMPNP_STATUS_OK;
-            g.flag = 0;
-            g.hist_len = 0;
-            g.n_evals = 0;
-            g.initial_set = 0;
-            for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) g.level_status[i] = 0;
-            g.level = 0;
-            g.it = 0;
-            if (MODE == kModeRefine) p.results[q].status = FMPNP_STATUS_INCOMPLETE;
-            if (MODE == kModeComputeCost)
-                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
-            else if (MODE == kModeFindInliers)
-                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, sc.units);
-            else if (p.n_levels > 0)  // multilevel: compute_cost on ALL channels first (model.py:182)
-                describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
-            else
-                describe_evaluation(g, qd.R0, qd.t0, kPhaseFirst, 1, 0, qd.C, p.use_ratio ? 1 : 0, p.loss_id, 0, sc.units);
-            enqueue_evaluation(sc, q);
-        }
-    }
+    // ---- queries are started (initial state + the tasks of their first evaluation) by whichever CTA comes by:
+    // one per pass through the loop below until none is left, so the launch makes progress with any number of
+    // resident CTAs (nothing waits for a CTA that has not been scheduled yet).
+    auto start_query = [&](int q) {
+        const QueryDev& qd = p.queries[q];
+        QueryState& g = sc.states[q];
+        for (int i = 0; i < 9; ++i) g.R[i] = g.Rn[i] = g.Rb[i] = qd.R0[i];
+        for (int i = 0; i < 3; ++i) g.t[i] = g.tn[i] = g.tb[i] = qd.t0[i];
+        for (int i = 0; i < 27; ++i) g.lin[i] = 0.0;
+        g.prev_cost = g.best_cost = NAN;
+        g.lambda = p.lambda0;
+        g.lr = 1.0;
+        g.initial_cost = NAN;
+        g.gathered = 0;
+        g.best_n = -1;
+        g.has_best = 0;
+        g.status = FMPNP_STATUS_OK;
+        g.flag = 0;
+        g.hist_len = 0;
+        g.n_evals = 0;
+        g.initial_set = 0;
+        for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) g.level_status[i] = 0;
+        g.level = 0;
+        g.it = 0;
+        if (MODE == kModeRefine) p.results[q].status = FMPNP_STATUS_INCOMPLETE;
+        if (MODE == kModeComputeCost)
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+        else if (MODE == kModeFindInliers)
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, sc.units);
+        else if (p.n_levels > 0)  // multilevel: compute_cost on ALL channels first (model.py:182)
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+        else
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseFirst, 1, 0, qd.C, p.use_ratio ? 1 : 0, p.loss_id, 0, sc.units);
+        enqueue_evaluation(sc, q);
+    };
 
     for (;;) {
         __syncthreads();
-        if (tid == 0) s_task = dequeue_task(sc, p.B);
+        if (tid == 0) {
+            if (ld_volatile_u32(sc.started) < (unsigned int)p.B) {
+                const unsigned int q = atomicAdd(sc.started, 1u);
+                if (q < (unsigned int)p.B) start_query((int)q);
+            }
+            s_task = dequeue_task(sc, p.B);
+        }
         __syncthreads();
         const int task = s_task;
         if (task < 0) break;

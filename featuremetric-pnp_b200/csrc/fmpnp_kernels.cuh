@@ -68,6 +68,7 @@ struct SchedDev {
     unsigned int* tail;         // next position to fill
     unsigned int* done;         // finished queries
     unsigned int* error;        // watchdog / protocol error flag
+    unsigned int* started;      // queries whose first evaluation has been queued
     uint32_t cap;               // power of two
     int32_t units;              // units per evaluation: 1, 2, 4, 8 or 16
     QueryState* states;         // [B]
