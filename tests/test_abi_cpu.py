@@ -76,3 +76,28 @@ def test_loss_mapping():
     assert fm.loss_id_of(functools.partial(hu.barron_loss, alpha=-1.0)) == (4, -1.0)
     with pytest.raises(fm.FmpnpError):
         fm.loss_id_of(lambda x: x)
+
+
+def test_header_is_plain_c_and_links_against_the_library(tmp_path):
+    """include/fmpnp.h compiles as C99 (no C++ or CUDA types in the boundary) and a C program that takes the
+    address of every declared entry point links against libfmpnp.so and runs (it only asks for the version and
+    the struct sizes: no compute without a GPU)."""
+    import shutil
+    import subprocess
+    fm = _ensure_built()
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    hdr = open(os.path.join(ROOT, "include", "fmpnp.h")).read()
+    names = sorted(set(re.findall(r"\b(fmpnp_[a-z_]+)\s*\(", re.sub(r"/\*.*?\*/", "", hdr, flags=re.S))))
+    src = tmp_path / "abi.c"
+    src.write_text('#include <stdio.h>\n#include "fmpnp.h"\n'
+                   "typedef void (*fn_t)(void);\nint main(void) {\n  fn_t fns[] = {%s};\n"
+                   '  printf("%%d %%d %%d %%d %%d %%d\\n", fmpnp_version(), fmpnp_struct_size(0), fmpnp_struct_size(1),\n'
+                   "         fmpnp_struct_size(2), (int)sizeof(fmpnp_problem), (int)(sizeof(fns) / sizeof(fns[0])));\n"
+                   "  return 0;\n}\n" % ", ".join("(fn_t)%s" % n for n in names))
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(fm.lib_path())
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                    str(src), "-o", str(exe), "-L", libdir, "-lfmpnp", "-Wl,-rpath," + libdir], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    assert int(out[0]) == 100 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)
