@@ -78,7 +78,10 @@ def compare(name, res, hist, o, b=0, use_ratio=False, sel=None):
 # wide channel counts: rows longer than a staging slot are split into channel chunks
 # ----------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("C,levels", [(1024, None), (640, None), (1024, [(512, 1024), (128, 512), (0, 128)]),
-                                      (2048, [(1024, 2048), (256, 1024), (0, 256)]), (516, None), (20, [(8, 20), (0, 8)])])
+                                      (2048, [(1024, 2048), (256, 1024), (0, 256)]),    # robotcar_feature_pyramid.gin:61
+                                      (1664, [(640, 1664), (128, 640), (0, 128)]),      # default_robotcar.gin:75
+                                      (1664, [(1152, 1664), (640, 1152), (384, 640), (128, 384), (0, 128)]),  # :76
+                                      (516, None), (20, [(8, 20), (0, 8)])])
 def test_wide_and_chunked_channels(C, levels, route):
     sc = synth().make_scene(21, N=200, C=C, Hf=16, Wf=16, im_width=128, im_height=128,
                             K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
