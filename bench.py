@@ -482,8 +482,9 @@ def main():
         per_q = sum(x[k].numel() * x[k].element_size() for x in ins[:1]
                     for k in ("pts3D", "feature_ref", "feature_map_query", "feature_grad_x", "feature_grad_y"))
         line["e2e_dropin"] = {"value": D / dt, "unit": UNIT + " per GPU", "h2d_bytes_per_query": int(per_q), "queries": D,
-                              "note": "model.sparseFeaturePnP.forward per query: pageable CPU float64 CHW tensors -> H2D -> "
-                                      "pack kernel -> refinement -> CPU float64 pose; wall clock, no inlier mask"}
+                              "note": "model.sparseFeaturePnP.forward per query: pageable CPU float64 CHW tensors -> float32 "
+                                      "in pinned staging (host threads) -> H2D -> pack kernel -> refinement -> CPU float64 "
+                                      "pose; wall clock, no inlier mask"}
         del ins
     near.__exit__(None, None, None)
     if "e2e" in line:

@@ -59,11 +59,40 @@ def _pack_map(m):
     src = m
     if src.dtype not in (torch.float32, torch.float64):
         src = src.double()
-    src = src.to(_device(), non_blocking=True).contiguous()
+    if src.device.type == "cpu":
+        src = _upload_as_float32(src)
+    else:
+        src = src.to(_device(), non_blocking=True).contiguous()
     out = torch.ops.fmpnp.pack_chw_to_hwc(src)
     _PACK_CACHE[key] = (m, out)  # keeping `m` alive keeps data_ptr unique
     while len(_PACK_CACHE) > _PACK_CACHE_MAX:
         _PACK_CACHE.popitem(last=False)
+    return out
+
+
+_STAGING = {}  # numel -> [next slot, [(pinned float32 buffer, event or None), ...]]
+
+
+def _upload_as_float32(src):
+    """CPU float64 / float32 map -> CUDA float32, same values as packing the float64 map on the device
+    (round-to-nearest either way).  The conversion runs on the host threads into a pinned buffer, so half the
+    bytes cross PCIe and the copy is a DMA instead of a pageable staged copy; three buffers per size rotate."""
+    dev = _device()
+    n = src.numel()
+    ring = _STAGING.get(n)
+    if ring is None:
+        if len(_STAGING) >= 4:
+            _STAGING.clear()
+        ring = _STAGING[n] = [0, [[torch.empty(n, dtype=torch.float32).pin_memory(), None] for _ in range(3)]]
+    slot = ring[1][ring[0]]
+    ring[0] = (ring[0] + 1) % len(ring[1])
+    if slot[1] is not None:
+        slot[1].synchronize()  # the upload that last used this buffer has left it
+    buf = slot[0].view(src.shape)
+    buf.copy_(src)
+    out = buf.to(dev, non_blocking=True)
+    slot[1] = torch.cuda.Event()
+    slot[1].record()
     return out
 
 

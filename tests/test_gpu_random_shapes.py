@@ -23,6 +23,8 @@ def draw_case(seed):
     cfg = dict(C=C, loss=LOSSES[int(r.randint(4))], lambda_=float(r.choice([0.0, 0.01, 1.0])),
                ratio=None if r.rand() < 0.5 else float(r.choice([0.5, 0.8, 0.95])), n_iters=int(r.randint(2, 7)),
                Ns=[int(x) for x in r.randint(1, n_hi, size=6)], map=int(r.choice([8, 16, 24])), levels=None)
+    if cfg["lambda_"] == 0.0:  # undamped Gauss-Newton needs a well-posed system: fewer than ~6 points make H
+        cfg["Ns"] = [max(n, 12) for n in cfg["Ns"]]  # singular and the step rounding noise (no parity to speak of)
     if C >= 8 and r.rand() < 0.4:  # coarse-to-fine channel slices (not necessarily multiples of 4)
         a, b = sorted(int(x) for x in r.choice(np.arange(1, C), size=2, replace=False))
         cfg["levels"] = [(b, C), (a, b), (0, a)]
