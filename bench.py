@@ -498,7 +498,10 @@ def main():
             v, dt = cpu_sample(args, cfg, nq, threads, scenes=scenes if nq <= len(scenes) else None)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "%d full-shape queries (seeds 0..%d of the same workload), one per thread, "
-                                              "%.1f s wall" % (nq, nq - 1, dt)}
+                                              "%.1f s wall" % (nq, nq - 1, dt),
+                                    "note": "C port of the reference's algorithm; the unmodified PyTorch reference needs "
+                                            "11.8 s per query of this shape with 8 threads (build container, "
+                                            "tests/golden/reference_cpu_timing.json) and cannot travel to this box"}
         except Exception as e:  # the baseline must never take the GPU number down with it
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "failed: %r" % (e,)}
