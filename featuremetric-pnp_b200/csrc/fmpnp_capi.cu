@@ -38,6 +38,7 @@ struct fmpnp_ctx {
     int ctas_per_sm = 0;
     int cluster = 0;
     int scheduler = 1;   // 1: task queue (default), 0: one CTA / cluster per query
+    int small_batch_clusters = 0;  // 1: a handful of queries (B <= 4) go to clusters even with the scheduler on
     int units = 0;       // tasks per evaluation (0 = automatic)
     QueryState* d_states = nullptr;
     double* d_part = nullptr;
@@ -46,7 +47,6 @@ struct fmpnp_ctx {
     uint32_t cap_queue = 0;
     unsigned int* d_sched = nullptr;  // head, tail, done, error
     int smem_configured = -1;
-    int nonportable = -1;
     Geometry_last last = {0, 0, 0, 0};
     int64_t launches = 0;
 };
@@ -159,38 +159,44 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
 }
 
 // Launch geometry.
-//   * Default: the task scheduler.  An evaluation is cut into U tasks (1..16) so that about three tasks per
-//     CTA slot exist; 2 CTAs per SM with a 96 KB staging ring each, or one CTA per SM with the whole shared
+//   * Default: the task scheduler.  An evaluation is cut into U tasks (1..128) so that about three tasks per
+//     CTA slot exist (tasks keep at least 64 points, 32 when the launch would not fill the SMs otherwise); 2 CTAs per SM with a 96 KB staging ring each, or one CTA per SM with the whole shared
 //     memory when there is at most one task per SM.
-//   * A handful of queries (B <= 4), an explicit cluster_size or FMPNP_SCHEDULER=0: one CTA, or a
-//     thread-block cluster of 2..16 CTAs, per query (the points are split, the normal equations combined
-//     through distributed shared memory).
+//   * An explicit cluster_size or FMPNP_SCHEDULER=0: one CTA, or a thread-block cluster of 2..16 CTAs, per
+//     query (the points are split, the normal equations combined through distributed shared memory).
 // FMPNP_RING_KB / FMPNP_MIN_DEPTH / FMPNP_CTAS_PER_SM / FMPNP_CLUSTER / FMPNP_UNITS override the choice
 // (tuning and tests only).
 struct Geometry {
     int grid, ring_bytes, ring_per_warp, min_depth, cluster, units;
 };
 
-int geometry(fmpnp_ctx* ctx, int32_t B, int requested_cluster, Geometry* g) {
+int32_t max_points(const fmpnp_problem* probs, int32_t B) {
+    int32_t n_max = 1;
+    for (int32_t b = 0; b < B; ++b)
+        if (probs[b].N > n_max) n_max = probs[b].N;
+    return n_max;
+}
+
+int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g) {
     int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
     int S = requested_cluster > 0 ? requested_cluster : ctx->cluster;
     // Task scheduler (default): an evaluation is cut into U tasks so that about three tasks per CTA slot are
     // available (load balance) while a task still gives every warp a whole batch; no clusters needed.
     // An explicit cluster_size (options / FMPNP_CLUSTER) or FMPNP_SCHEDULER=0 selects the per-query path.
-    // A handful of queries (B * 16 tasks would leave half of the SMs idle anyway) go to clusters of 16: the
-    // cluster combines its sums through distributed shared memory, without a global-memory round trip per
-    // evaluation (2.31 vs 2.42 ms for one cfg3 query), and its ratio test needs no serial pass.
+    // (FMPNP_SMALL_BATCH_CLUSTERS=1 sends B <= 4 to clusters as well: that was faster while an evaluation could
+    // only be cut into 16 tasks; with 128 the scheduler refines one cfg3 query in 0.73 ms against 1.99 ms.)
     bool tasks = ctx->scheduler == 1 && S == 0;
-    if (tasks && ctx->units <= 0 && (int64_t)B * kRanges * 2 <= ctx->sm_count) tasks = false;
+    if (tasks && ctx->units <= 0 && ctx->small_batch_clusters && (int64_t)B * 32 <= ctx->sm_count) tasks = false;
     int U = 1;
     if (tasks) {
         U = ctx->units;
         if (U <= 0) {
-            U = 1;
-            while (U < kRanges && (int64_t)B * U < 3 * 2 * (int64_t)ctx->sm_count) U *= 2;
+            U = 1;  // ... with at least 64 points per task, or 32 when the tasks would not even fill the CTA slots
+            while (U < kRanges && (int64_t)B * U < 3 * 2 * (int64_t)ctx->sm_count && (int64_t)n_max >= 128 * (int64_t)U) U *= 2;
+            while (U < kRanges && (int64_t)B * U < 2 * (int64_t)ctx->sm_count && (int64_t)n_max >= 64 * (int64_t)U) U *= 2;
         }
-        if (U != 1 && U != 2 && U != 4 && U != 8 && U != 16)
-            return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "FMPNP_UNITS must be 1, 2, 4, 8 or 16; got %d", U);
+        if (U < 1 || U > kRanges || (U & (U - 1)) != 0)
+            return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "FMPNP_UNITS must be a power of two between 1 and %d; got %d", kRanges, U);
         S = 1;
     }
     g->units = tasks ? U : 0;
@@ -210,20 +216,19 @@ int geometry(fmpnp_ctx* ctx, int32_t B, int requested_cluster, Geometry* g) {
         int ps = per_sm > 0 ? (per_sm > 2 ? 2 : per_sm) : ((work * S <= ctx->sm_count) ? 1 : 2);
         int r = ring > 0 ? ring : (ps == 1 ? budget : 96 * 1024);
         if (r > budget) r = budget;
-        if (r < 64 * 1024) r = 64 * 1024;  // the reductions use the ring as scratch (28 x 288 doubles)
+        if (r < 72 * 1024) r = 72 * 1024;  // the reductions use a warp's slice as scratch (kWarpScratchDoubles)
         const int per_warp = (r / kWarps) & ~127;
         if (per_warp < 2 * 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", r);
         r = per_warp * kWarps;
-        if (ctx->smem_configured < r) {
-            FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(r));
-            ctx->smem_configured = r;
+        // The kernels' function attributes belong to the process (per device), not to a context: every context
+        // sets the same values -- the largest ring any launch may ask for, non-portable cluster sizes allowed --
+        // so that one context never invalidates what another one relies on.
+        if (ctx->smem_configured < 0) {
+            FMPNP_CUDA(ctx, refine_set_max_dynamic_smem(((budget / kWarps) & ~127) * kWarps));
+            FMPNP_CUDA(ctx, refine_allow_nonportable_clusters(1));
+            ctx->smem_configured = 1;
         }
         int clusters = ctx->sm_count * ps / S;
-        const int want_np = S > 8 ? 1 : 0;
-        if (ctx->nonportable != want_np) {
-            FMPNP_CUDA(ctx, refine_allow_nonportable_clusters(want_np));
-            ctx->nonportable = want_np;
-        }
         if (S > 1) {
             const int fit = max_active_clusters(S, r);
             if (fit < 1) {  // such a cluster cannot be scheduled: halve it
@@ -269,10 +274,10 @@ int prepare_tasks(fmpnp_ctx* ctx, int32_t B, const Geometry& g, LaunchParams& lp
         if (ctx->d_part) FMPNP_CUDA(ctx, cudaFree(ctx->d_part));
         ctx->d_part = nullptr;
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_states, (size_t)B * sizeof(QueryState)));
-        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_part, (size_t)B * kRanges * 32 * sizeof(double)));
+        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_part, (size_t)B * kRanges * 32 * sizeof(double)));  // 32 KB per query
         ctx->cap_states = (size_t)B;
     }
-    uint64_t want = 2ull * (uint64_t)B * kRanges;  // at most B * units tasks are ever queued at once
+    uint64_t want = 2ull * (uint64_t)B * (uint64_t)g.units;  // at most B * units tasks are ever queued at once
     uint32_t cap = 1024;
     while (cap < want) cap <<= 1;
     if (cap > ctx->cap_queue) {
@@ -337,6 +342,7 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     ctx->cluster = env_int("FMPNP_CLUSTER", 0);
     ctx->scheduler = env_int("FMPNP_SCHEDULER", 1);
     ctx->units = env_int("FMPNP_UNITS", 0);
+    ctx->small_batch_clusters = env_int("FMPNP_SMALL_BATCH_CLUSTERS", 0);
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     *out = ctx;
     return FMPNP_SUCCESS;
@@ -399,7 +405,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     Geometry g;
-    int rc = geometry(ctx, B, o->cluster_size, &g);
+    int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g);
     if (rc) return rc;
     int32_t n_max;
     rc = stage(ctx, probs, B, g.units > 0 ? B : g.grid, &n_max, stream);
@@ -457,7 +463,7 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     Geometry g;
-    int rc = geometry(ctx, B, 0, &g);
+    int rc = geometry(ctx, B, max_points(probs, B), 0, &g);
     if (rc) return rc;
     int32_t n_max;
     rc = stage(ctx, probs, B, g.units > 0 ? B : g.grid, &n_max, stream);
@@ -493,7 +499,7 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     Geometry g;
-    int rc = geometry(ctx, B, 0, &g);
+    int rc = geometry(ctx, B, max_points(probs, B), 0, &g);
     if (rc) return rc;
     int32_t n_max;
     rc = stage(ctx, probs, B, g.units > 0 ? B : g.grid, &n_max, stream);

@@ -51,7 +51,7 @@ struct __align__(16) Shared {
     double ev[28];        // last evaluation: H (21), g (6), sum of rho
     double A[36], b[8];   // solver workspace
     double red[kWarps][32];
-    double tree[5][32];   // pairwise-tree stack over this CTA's point ranges
+    double wtot[kWarps][28];  // per-warp totals of the ranges a warp owns (reduce_points), group totals (combine_parts)
     double climit;
     double cpart[2][32];  // this CTA's partial sums, read by the other CTAs of the cluster (double-buffered)
     double prev_cost, best_cost, lambda, lr, ev_cost, limit, initial_cost;
@@ -96,6 +96,7 @@ struct EvalCtx {
     int32_t range_len;                 // points per fixed reduction range (kRanges ranges cover N)
     int32_t csize, crank;              // thread-block cluster working on this query (or: tasks of this evaluation)
     double* part_out;                  // task scheduler: this task's partial sums go here (global), no combine
+    bool limit_given;                  // task scheduler: sh.limit already holds the ratio-test limit
 };
 
 // Staging geometry of one evaluation.
@@ -276,6 +277,9 @@ __device__ __forceinline__ void acc4(uint32_t aF, uint32_t aGx, uint32_t aGy, ui
 }
 
 // FULL whole-warp copies (512 B each) of each of the ROWS rows s[r] to dst + r * rowB
+// points a warp projects at a time, given the points its CTA streams in this evaluation
+__device__ __forceinline__ int batch_width(int span) { return span > 128 ? 32 : (span > 64 ? 16 : (span > 32 ? 8 : 4)); }
+
 template <int ROWS, int FULL>
 __device__ __forceinline__ void copy_rows_full(uint32_t dst, const char* const (&s)[4], uint32_t rowB) {
 #pragma unroll
@@ -306,9 +310,11 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
     const uint32_t slot_bytes = (uint32_t)c.slot_bytes;
     const int32_t* bcell = &sh.bl_cell[warp][0][0];  // [2][32]
     const int32_t* bn = &sh.bl_n[warp][0][0];
-    // batches of 32 points owned by this warp: base = n0 + (warp + b * kWarps) * 32
-    const int first = c.n0 + warp * 32;
-    const int nb = first < N ? (N - first + kWarps * 32 - 1) / (kWarps * 32) : 0;
+    // batches of BW points owned by this warp: base = n0 + (warp + b * kWarps) * BW.  BW = 32 unless the CTA
+    // has so few points (a small task of the scheduler) that narrower batches are needed to occupy every warp.
+    const int BW = batch_width(N - c.n0);
+    const int first = c.n0 + warp * BW;
+    const int nb = first < N ? (N - first + kWarps * BW - 1) / (kWarps * BW) : 0;
     if (nb == 0) return;
 
     // row base pointers with this lane's 16-byte piece folded in
@@ -320,9 +326,9 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
 
     // projects batch b and leaves its supported points compacted in buffer `buf`; returns their count
     auto load_batch = [&](int b, int buf) -> int {
-        const int n = first + b * kWarps * 32 + lane;
+        const int n = first + b * kWarps * BW + lane;
         int cell = -1;
-        if (n < N) cell = project_and_flag(c, R, t, n);
+        if (lane < BW && n < N) cell = project_and_flag(c, R, t, n);
         const unsigned mask = __ballot_sync(0xffffffffu, cell >= 0);
         if (cell >= 0) {
             const int rank = __popc(mask & ((1u << lane) - 1u));
@@ -508,11 +514,12 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
 
     if (!c.aligned) {
         // ---------------- generic path: every warp projects its own 32 points, loads directly
-        for (int base = c.n0 + warp * 32; base < N; base += kWarps * 32) {
+        const int BW = batch_width(N - c.n0);
+        for (int base = c.n0 + warp * BW; base < N; base += kWarps * BW) {
             const int n = base + lane;
             int cell = -1;
-            if (n < N) cell = project_and_flag(c, R, t, n);
-            for (int j = 0; j < 32; ++j) {
+            if (lane < BW && n < N) cell = project_and_flag(c, R, t, n);
+            for (int j = 0; j < BW; ++j) {
                 const int cj = __shfl_sync(0xffffffffu, cell, j);
                 if (cj < 0) continue;
                 const int nj = base + j;
@@ -546,52 +553,15 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
 }
 
 // ---------------------------------------------------------------------------------------------
-// Deterministic reductions.  The points of a query are cut into kRanges fixed ranges (the same for
-// every launch geometry); a range is summed by a fixed tree (threads stride the range, lanes by
-// butterfly, warps in index order) and the range totals are added pairwise, first inside the
-// CTA, then across the cluster.  A CTA owns kRanges / cluster_size consecutive ranges, so the
-// result is bit-identical for every cluster size, batch size and staging-ring geometry.
+// Deterministic reductions.  The points of a query are cut into kRanges = 128 fixed ranges (the same
+// for every launch geometry).  A range is summed by ONE warp in a fixed order (lanes stride the range,
+// then a transposition through the warp's idle slice of the staging ring and a pairwise tree over the
+// 32 lanes); range totals are added pairwise along the aligned binary tree over the range index: first
+// over the consecutive ranges a warp owns, then over the warps of the CTA, then over the CTAs of the
+// cluster or the tasks of the evaluation.  Every owner holds an aligned power-of-two run of ranges, so
+// the result is bit-identical for every cluster size, task count, batch size and ring geometry.
 // ---------------------------------------------------------------------------------------------
-// Sums v[0..NV) / iv[0..2) over the block through the (idle) staging ring: every thread stores its
-// partials as a column of A[NV][kThreads]; warp w then adds rows w, w + kWarps, ... (each lane 9
-// entries in order, then a butterfly).  Afterwards lane 0 of warp (i % kWarps) holds total i
-// (returned there, 0 elsewhere) and warp 0, lanes 0 / 1 hold the integer totals in `itot`.
-// The caller separates consecutive calls by a __syncthreads().
-constexpr int kSumStride = kThreads;
-template <int NV>
-__device__ __forceinline__ void block_sum(double (&v)[NV], int32_t (&iv)[2], Shared& sh, double* scratch,
-                                          double (&tot)[(NV + kWarps - 1) / kWarps], int32_t& itot) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) scratch[i * kSumStride + tid] = v[i];
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) iv[i] += __shfl_xor_sync(0xffffffffu, iv[i], off);
-    }
-    if (lane == 0) {
-        sh.red_i[warp][0] = iv[0];
-        sh.red_i[warp][1] = iv[1];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < (NV + kWarps - 1) / kWarps; ++k) {
-        const int i = warp + k * kWarps;
-        double s = 0.0;
-        if (i < NV) {
-            const double* row = scratch + i * kSumStride + lane;
-            s = row[0];
-#pragma unroll
-            for (int j = 1; j < kWarps; ++j) s = __dadd_rn(s, row[32 * j]);
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) s = __dadd_rn(s, shfl_xor_f64(s, off));
-        tot[k] = s;
-    }
-    itot = 0;
-    if (warp == 0 && lane < 2)
-        for (int w = 0; w < kWarps; ++w) itot += sh.red_i[w][lane];
-}
+// (kLaneStride, kWarpScratchDoubles: fmpnp_kernels.cuh -- the host sizes the ring so that a warp's slice holds them)
 
 // Combines the per-CTA values every CTA of the cluster left in its own Shared::cpart[par] /
 // cpart_i[par]: all CTAs read all partials through distributed shared memory and add them in
@@ -605,14 +575,14 @@ __device__ __forceinline__ void cluster_combine(Shared& sh, int csize, int32_t& 
     cl.sync();
     const int tid = threadIdx.x;
     if (tid < nv) {
-        double v[kRanges];
+        double v[kMaxCluster];
 #pragma unroll
-        for (int r = 0; r < kRanges; ++r) v[r] = r < csize ? *cl.map_shared_rank(&sh.cpart[par][tid], r) : 0.0;
+        for (int r = 0; r < kMaxCluster; ++r) v[r] = r < csize ? *cl.map_shared_rank(&sh.cpart[par][tid], r) : 0.0;
 #pragma unroll
-        for (int w = 1; w < kRanges; w <<= 1) {
+        for (int w = 1; w < kMaxCluster; w <<= 1) {
             if (w < csize) {
 #pragma unroll
-                for (int i = 0; i + w < kRanges; i += 2 * w) v[i] = MAX ? fmax(v[i], v[i + w]) : __dadd_rn(v[i], v[i + w]);
+                for (int i = 0; i + w < kMaxCluster; i += 2 * w) v[i] = MAX ? fmax(v[i], v[i + w]) : __dadd_rn(v[i], v[i + w]);
             }
         }
         out[tid] = v[0];
@@ -633,6 +603,43 @@ __device__ __forceinline__ void cluster_combine(Shared& sh, int csize, int32_t& 
 // Per-point phase: robust loss, ratio test, contraction with the projection Jacobian, sums.
 // Leaves sh.ev[0..27], sh.ev_count (survivors), sh.ev_nsup (supported) and sh.ev_cost (mean rho).
 // ---------------------------------------------------------------------------------------------
+// max |rho| over the supported points [c.n0, c.n1) of this CTA and whether any is NaN (torch.max propagates NaN):
+// the ingredients of ratio_threshold_feature_errors' limit (model.py:120-129).  Valid in thread 0 after the call.
+__device__ __forceinline__ void block_ratio_max(const EvalCtx& c, Shared& sh, double& mm, int& nf) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    double m = -INFINITY;
+    int nanf = 0;
+    for (int n = c.n0 + tid; n < c.n1; n += kThreads) {
+        if (!__ldcg(c.supp + n)) continue;  // .cg: records may have been written by another CTA (task scheduler)
+        const double x = __dmul_rn(0.5, __ldcg(c.rec + (size_t)n * kRecDoubles));
+        double rho = x, w = 1.0;
+        if (c.ratio_mode == 1) robust_loss(c.loss_id, c.alpha, x, rho, w);
+        const double a = fabs(rho);
+        if (a != a) nanf = 1;
+        m = fmax(m, a);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        m = fmax(m, shfl_xor_f64(m, off));
+        nanf |= __shfl_xor_sync(0xffffffffu, nanf, off);
+    }
+    if (lane == 0) {
+        sh.red[warp][0] = m;
+        sh.red_i[warp][0] = nanf;
+    }
+    __syncthreads();
+    mm = -INFINITY;
+    nf = 0;
+    if (tid == 0) {
+        mm = sh.red[0][0];
+        nf = sh.red_i[0][0];
+        for (int w = 1; w < kWarps; ++w) {
+            mm = fmax(mm, sh.red[w][0]);
+            nf |= sh.red_i[w][0];
+        }
+    }
+}
+
 template <bool GRAD>
 __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     const QueryDev& q = *c.q;
@@ -640,36 +647,11 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     const int warp = tid >> 5, lane = tid & 31;
     const bool use_ratio = c.ratio_mode != 0;
 
-    if (use_ratio) {
-        // ratio_threshold_feature_errors (model.py:120-129): limit = max |rho| * threshold
-        double m = -INFINITY;
-        int nanf = 0;
-        for (int n = c.n0 + tid; n < c.n1; n += kThreads) {
-            if (!__ldcg(c.supp + n)) continue;  // .cg: records may have been written by another CTA (task scheduler)
-            const double x = __dmul_rn(0.5, __ldcg(c.rec + (size_t)n * kRecDoubles));
-            double rho = x, w = 1.0;
-            if (c.ratio_mode == 1) robust_loss(c.loss_id, c.alpha, x, rho, w);
-            const double a = fabs(rho);
-            if (a != a) nanf = 1;
-            m = fmax(m, a);
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            m = fmax(m, shfl_xor_f64(m, off));
-            nanf |= __shfl_xor_sync(0xffffffffu, nanf, off);
-        }
-        if (lane == 0) {
-            sh.red[warp][0] = m;
-            sh.red_i[warp][0] = nanf;
-        }
-        __syncthreads();
+    if (use_ratio && !c.limit_given) {
+        double mm;
+        int nf;
+        block_ratio_max(c, sh, mm, nf);
         if (tid == 0) {
-            double mm = sh.red[0][0];
-            int nf = sh.red_i[0][0];
-            for (int w = 1; w < kWarps; ++w) {
-                mm = fmax(mm, sh.red[w][0]);
-                nf |= sh.red_i[w][0];
-            }
             if (c.csize > 1) {
                 sh.cpart[rp.cpar][0] = mm;
                 sh.cpart_i[rp.cpar][0] = nf;
@@ -686,80 +668,112 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     const double limit = use_ratio ? sh.limit : 0.0;
 
     const double fx = q.K[0], fy = q.K[4];
-    const int per = c.range_len;  // points per fixed range
-    const int r_first = c.crank * (kRanges / c.csize);
-    const int r_count = kRanges / c.csize;
-    int32_t tot_i = 0;  // warp 0, lanes 0 / 1: survivors / supported of this CTA
-    for (int rr = 0; rr < r_count; ++rr) {
-        const int r0 = min(q.N, (r_first + rr) * per), r1 = min(q.N, r0 + per);
-        double acc[28];
+    const int per = c.range_len;              // points per fixed range
+    const int nr = kRanges / c.csize;         // ranges this CTA owns: an aligned power-of-two run
+    const int r_first = c.crank * nr;
+    const int rpw = nr >= kWarps ? nr / kWarps : 1;  // consecutive ranges per warp ...
+    const int wact = nr >= kWarps ? kWarps : nr;     // ... of the warps that own any
+    double* const wscr = reinterpret_cast<double*>(c.ring + (size_t)warp * c.ring_per_warp);  // idle ring slice
+    double* const stack = wscr + 28 * kLaneStride;
+    int32_t cnt[2] = {0, 0};  // survivors, supported (this lane, all its ranges)
+    if (warp < wact) {
+        for (int rr = 0; rr < rpw; ++rr) {
+            const int r0 = min(q.N, (r_first + warp * rpw + rr) * per), r1 = min(q.N, r0 + per);
+            double acc[28];
 #pragma unroll
-        for (int i = 0; i < 28; ++i) acc[i] = 0.0;
-        int32_t cnt[2] = {0, 0};  // survivors, supported
-        for (int n = r0 + tid; n < r1; n += kThreads) {
-            const bool sup = __ldcg(c.supp + n) != 0;
-            bool keep = false;
-            if (sup) {
-                ++cnt[1];
-                const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
-                const double2 rc0 = __ldcg(r);
-                const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
-                double rho = x, w = 1.0;
-                if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
-                keep = !use_ratio || (fabs(rho) < limit);
-                if (keep) {
-                    ++cnt[0];
-                    acc[27] = __dadd_rn(acc[27], rho);
-                    if (GRAD) {
-                        const double2 rc1 = __ldcg(r + 1), rc2 = __ldcg(r + 2);
-                        const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
-                                                      q.im_w, q.im_h);
-                        contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
+            for (int i = 0; i < 28; ++i) acc[i] = 0.0;
+            for (int n = r0 + lane; n < r1; n += 32) {
+                const bool sup = __ldcg(c.supp + n) != 0;
+                bool keep = false;
+                if (sup) {
+                    ++cnt[1];
+                    const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+                    const double2 rc0 = __ldcg(r);
+                    const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
+                    double rho = x, w = 1.0;
+                    if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
+                    keep = !use_ratio || (fabs(rho) < limit);
+                    if (keep) {
+                        ++cnt[0];
+                        acc[27] = __dadd_rn(acc[27], rho);
+                        if (GRAD) {
+                            const double2 rc1 = __ldcg(r + 1), rc2 = __ldcg(r + 2);
+                            const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
+                                                          q.im_w, q.im_h);
+                            contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
+                        }
                     }
                 }
+                if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
+                if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
             }
-            if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
-            if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
-        }
-        __syncthreads();  // the scratch columns of the previous range have been consumed
-        int32_t it;
-        double tot[4];
-        block_sum<28>(acc, cnt, sh, reinterpret_cast<double*>(c.ring), tot, it);
-        tot_i += it;
-        if (lane == 0) {  // this thread owns totals i = warp + k * kWarps: pairwise tree over the CTA's ranges
+            // the 32 lane partials of each of the 28 sums -> lane i (transposition), pairwise tree over the lanes
+            __syncwarp();  // the rows of the previous range have been read
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int i = warp + k * kWarps;
-                if (i >= 28) continue;
-                double x = tot[k];
+            for (int i = 0; i < 28; ++i) wscr[i * kLaneStride + lane] = acc[i];
+            __syncwarp();
+            if (lane < 28) {
+                const double* row = wscr + lane * kLaneStride;
+                double x[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) x[k] = __dadd_rn(row[2 * k], row[2 * k + 1]);
+#pragma unroll
+                for (int w = 1; w < 16; w <<= 1) {
+#pragma unroll
+                    for (int k = 0; k + w < 16; k += 2 * w) x[k] = __dadd_rn(x[k], x[k + w]);
+                }
+                double tot = x[0];
                 int level = 0;
-                for (int kk = rr; kk & 1; kk >>= 1) {  // binary-counter stack
-                    x = __dadd_rn(sh.tree[level][i], x);
+                for (int kk = rr; kk & 1; kk >>= 1) {  // binary-counter stack: pairwise tree over this warp's ranges
+                    tot = __dadd_rn(stack[level * 28 + lane], tot);
                     ++level;
                 }
-                sh.tree[level][i] = x;
-                if (rr == r_count - 1) {  // r_count is a power of two: the total sits on top of the stack
-                    if (c.part_out)
-                        c.part_out[i] = x;
-                    else if (c.csize > 1)
-                        sh.cpart[rp.cpar][i] = x;
-                    else
-                        sh.ev[i] = x;
-                }
+                stack[level * 28 + lane] = tot;
+                if (rr == rpw - 1) sh.wtot[warp][lane] = tot;  // rpw is a power of two: the total is on top
             }
         }
     }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) cnt[i] += __shfl_xor_sync(0xffffffffu, cnt[i], off);
+    }
+    if (lane == 0) {
+        sh.red_i[warp][0] = cnt[0];
+        sh.red_i[warp][1] = cnt[1];
+    }
+    __syncthreads();
     int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
+    if (tid < 28) {  // pairwise tree over the warps that own ranges
+        double v[kWarps];
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) v[w] = w < wact ? sh.wtot[w][tid] : 0.0;
+#pragma unroll
+        for (int w = 1; w < kWarps; w <<= 1) {
+            if (w < wact) {
+#pragma unroll
+                for (int k = 0; k + w < kWarps; k += 2 * w) v[k] = __dadd_rn(v[k], v[k + w]);
+            }
+        }
+        if (c.part_out)
+            c.part_out[tid] = v[0];
+        else if (c.csize > 1)
+            sh.cpart[rp.cpar][tid] = v[0];
+        else
+            sh.ev[tid] = v[0];
+    } else if (tid >= 32 && tid < 34) {
+        int32_t tot_i = 0;
+        for (int w = 0; w < kWarps; ++w) tot_i += sh.red_i[w][tid - 32];
+        if (c.part_out)
+            reinterpret_cast<long long*>(c.part_out)[28 + (tid - 32)] = tot_i;
+        else if (c.csize > 1)
+            sh.cpart_i[rp.cpar][tid - 32] = tot_i;
+        else
+            iout[tid - 32] = tot_i;
+    }
     if (c.part_out) {  // the CTA that completes the evaluation combines the tasks' partials (combine_parts)
-        if (warp == 0 && lane < 2) reinterpret_cast<long long*>(c.part_out)[28 + lane] = tot_i;
         __syncthreads();
         return;
-    }
-    if (warp == 0 && lane < 2) {
-        if (c.csize > 1)
-            sh.cpart_i[rp.cpar][lane] = tot_i;
-        else
-            iout[lane] = tot_i;
     }
     if (c.csize > 1)
         cluster_combine<false>(sh, c.csize, rp.cpar, 28, sh.ev, 2, iout);
@@ -897,8 +911,9 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.csize = csize;
         c.crank = crank;
         c.part_out = nullptr;
+        c.limit_given = false;
         {
-            const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
+            const int per = max(1, (q.N + kRanges - 1) / kRanges);
             c.range_len = per;
             c.n0 = min(q.N, crank * (kRanges / csize) * per);
             c.n1 = min(q.N, (crank + 1) * (kRanges / csize) * per);
@@ -1234,29 +1249,47 @@ __device__ __forceinline__ void describe_evaluation(QueryState& g, const double*
     g.ev_ratio_mode = ratio_mode;
     g.ev_loss = loss;
     g.ev_hist = hist_entry;
+    g.ev_round = 0;
     g.pending = units;
 }
 
-// Adds the partial sums the `units` tasks of an evaluation left in global memory, in the order
-// cluster_combine uses (pairwise tree over the tasks): sh.ev[0..27], ev_count, ev_nsup, ev_cost.
+// Adds the partial sums the `units` (a power of two, up to 128) tasks of an evaluation left in global memory
+// along the same aligned pairwise tree: groups of up to 16 consecutive tasks by 8 x 28 threads, then the groups.
+// Leaves sh.ev[0..27], ev_count, ev_nsup, ev_cost.
 __device__ __forceinline__ void combine_parts(Shared& sh, const double* part, int units) {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, grp = tid >> 5, i = tid & 31;
+    const int in_group = units < 16 ? units : 16, groups = units < 16 ? 1 : units >> 4;
+    if (i < 28 && grp < groups) {
+        const double* src = part + (size_t)(grp * 16) * kPartStride + i;
+        double v[16];
+#pragma unroll
+        for (int r = 0; r < 16; ++r) v[r] = r < in_group ? __ldcg(src + r * kPartStride) : 0.0;
+#pragma unroll
+        for (int w = 1; w < 16; w <<= 1) {
+            if (w < in_group) {
+#pragma unroll
+                for (int k = 0; k + w < 16; k += 2 * w) v[k] = __dadd_rn(v[k], v[k + w]);
+            }
+        }
+        sh.wtot[grp][i] = v[0];
+    }
+    __syncthreads();
     if (tid < 28) {
-        double v[kRanges];
+        double v[kWarps];
 #pragma unroll
-        for (int r = 0; r < kRanges; ++r) v[r] = r < units ? __ldcg(part + r * kPartStride + tid) : 0.0;
+        for (int g = 0; g < kWarps; ++g) v[g] = g < groups ? sh.wtot[g][tid] : 0.0;
 #pragma unroll
-        for (int w = 1; w < kRanges; w <<= 1) {
-            if (w < units) {
+        for (int w = 1; w < kWarps; w <<= 1) {
+            if (w < groups) {
 #pragma unroll
-                for (int i = 0; i + w < kRanges; i += 2 * w) v[i] = __dadd_rn(v[i], v[i + w]);
+                for (int k = 0; k + w < kWarps; k += 2 * w) v[k] = __dadd_rn(v[k], v[k + w]);
             }
         }
         sh.ev[tid] = v[0];
     } else if (tid >= 32 && tid < 34) {
-        long long s = 0;
-        for (int r = 0; r < units; ++r) s += __ldcg(reinterpret_cast<const long long*>(part + r * kPartStride) + 28 + (tid - 32));
-        (&sh.ev_count)[tid - 32] = (int32_t)s;
+        long long sum = 0;
+        for (int r = 0; r < units; ++r) sum += __ldcg(reinterpret_cast<const long long*>(part + (size_t)r * kPartStride) + 28 + (tid - 32));
+        (&sh.ev_count)[tid - 32] = (int32_t)sum;
     }
     __syncthreads();
     if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;
@@ -1340,6 +1373,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.csize = 1;
         c.crank = 0;
         c.part_out = nullptr;
+        c.limit_given = false;
         c.c0 = gv.ev_c0;
         c.Cl = gv.ev_Cl;
         c.loss_id = gv.ev_loss;
@@ -1355,7 +1389,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.h_kept = nullptr;
         if (hist_entry >= 0) hist_slices(p, qi, hist_entry, c);
         {
-            const int per = (((q.N + kRanges - 1) / kRanges) + 31) & ~31;
+            const int per = max(1, (q.N + kRanges - 1) / kRanges);
             const int rpu = kRanges / sc.units;  // fixed ranges per task
             c.range_len = per;
             c.n0 = min(q.N, u * rpu * per);
@@ -1363,25 +1397,42 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         }
         __syncthreads();
 
-        // ---- the task: stream this run of points, one record per supported point
-        rp.pos = 0;
-        if (grad) {
-            set_geometry(c, 4);
-            stream_points<true>(c, evpose, evpose + 9, sh, rp);
-        } else {
-            set_geometry(c, 2);
-            stream_points<false>(c, evpose, evpose + 9, sh, rp);
+        // ---- the task.  Round 0 streams this run of points (one record per supported point).  Then the
+        // per-point phase of the task's own ranges: without a ratio test it needs nothing from the other tasks
+        // and follows at once (28 + 2 partial sums); with one, the limit is a maximum over ALL points, so
+        // round 0 only leaves the task's max |rho|, the CTA that completes the round publishes the limit and
+        // queues the tasks again (round 1: sums only, the records come from L2).
+        const int round = gv.ev_round;
+        const bool multi = sc.units > 1, ratio = c.ratio_mode != 0;
+        double* const parts = sc.part + (size_t)qi * sc.units * kPartStride;
+        if (round == 0) {
+            rp.pos = 0;
+            if (grad) {
+                set_geometry(c, 4);
+                stream_points<true>(c, evpose, evpose + 9, sh, rp);
+            } else {
+                set_geometry(c, 2);
+                stream_points<false>(c, evpose, evpose + 9, sh, rp);
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        // Without a ratio test the per-point phase needs nothing from the other tasks: this task sums its own
-        // ranges and leaves 28 + 2 partials.  With one, the limit is a maximum over ALL points, so the CTA
-        // that completes the evaluation runs the per-point phase over the whole query.
-        const bool split = c.ratio_mode == 0 && sc.units > 1;
-        double* const parts = sc.part + (size_t)qi * kRanges * kPartStride;
-        if (split) {
+        if (multi && ratio && round == 0) {
+            double mm;
+            int nf;
+            block_ratio_max(c, sh, mm, nf);
+            if (tid == 0) {
+                parts[u * kPartStride + 30] = mm;
+                reinterpret_cast<long long*>(parts)[u * kPartStride + 31] = nf;
+            }
+        } else if (multi) {
+            if (ratio) {
+                if (tid == 0) sh.limit = gv.ev_limit;
+                __syncthreads();
+            }
             c.csize = sc.units;
             c.crank = u;
             c.part_out = parts + u * kPartStride;
+            c.limit_given = ratio;
             if (grad)
                 reduce_points<true>(c, evpose, evpose + 9, sh, rp);
             else
@@ -1389,6 +1440,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             c.csize = 1;
             c.crank = 0;
             c.part_out = nullptr;
+            c.limit_given = false;
         }
         if (tid == 0) {
             __threadfence();  // records / partials before the count
@@ -1398,12 +1450,28 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         __syncthreads();
         if (!s_last) continue;
 
+        if (multi && ratio && round == 0) {  // every task has streamed: limit = max |rho| * threshold, then round 1
+            if (tid == 0) {
+                double mm = -INFINITY;
+                long long nf = 0;
+                for (int r = 0; r < sc.units; ++r) {
+                    mm = fmax(mm, __ldcg(parts + r * kPartStride + 30));
+                    nf |= __ldcg(reinterpret_cast<const long long*>(parts) + r * kPartStride + 31);
+                }
+                g.ev_limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
+                g.ev_round = 1;
+                g.pending = sc.units;
+                enqueue_evaluation(sc, qi);
+            }
+            continue;
+        }
+
         // ---- this CTA completed the evaluation: total the query, advance its state machine
         c.n0 = 0;
         c.n1 = q.N;
         if (tid == 0) load_state(sh, gv);
         __syncthreads();
-        if (split)
+        if (multi)
             combine_parts(sh, parts, sc.units);
         else if (grad)
             reduce_points<true>(c, evpose, evpose + 9, sh, rp);

@@ -11,7 +11,10 @@ namespace fmpnp {
 constexpr int kWarps = 8;                         // each streams its own points through its slice of the ring
 constexpr int kThreads = kWarps * 32;             // 256
 constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
-constexpr int kRanges = 16;                       // fixed reduction ranges per query == max cluster size
+constexpr int kRanges = 128;                      // fixed reduction ranges per query == max tasks per evaluation
+constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
+constexpr int kLaneStride = 33;                   // reduction scratch: doubles per transposed row (conflict-free columns)
+constexpr int kWarpScratchDoubles = 28 * kLaneStride + 8 * 28;  // per warp: transposition + pairwise-tree stack
 constexpr int kMaxDepth = 8;                      // max slots per sub-ring
 
 enum KernelMode { kModeRefine = 0, kModeComputeCost = 1, kModeFindInliers = 2 };
@@ -53,13 +56,14 @@ struct __align__(16) QueryState {
     double lin[27];       // accepted linearisation
     double prev_cost, best_cost, lambda, lr, initial_cost;
     double evR[9], evt[3];  // pose of the evaluation in flight
+    double ev_limit;        // its ratio-test limit (published between round 0 and round 1)
     long long gathered;
     int32_t best_n, has_best, status, flag, hist_len, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
     int32_t phase, level, it;
     int32_t ev_grad, ev_c0, ev_Cl, ev_ratio_mode, ev_loss, ev_hist;  // the evaluation in flight
     int32_t pending;      // its units still running
-    int32_t pad;
+    int32_t ev_round;     // 0: streaming round, 1: summing round of an evaluation with a ratio test
 };
 
 struct SchedDev {
@@ -70,9 +74,9 @@ struct SchedDev {
     unsigned int* error;        // watchdog / protocol error flag
     unsigned int* started;      // queries whose first evaluation has been queued
     uint32_t cap;               // power of two
-    int32_t units;              // units per evaluation: 1, 2, 4, 8 or 16
+    int32_t units;              // tasks per evaluation: a power of two, 1..128
     QueryState* states;         // [B]
-    double* part;               // [B][16][32] partial sums of the tasks of the evaluation in flight
+    double* part;               // [B][units][32] partial sums (+ max |rho|, NaN flag) of the tasks of the evaluation in flight
 };
 
 struct LaunchParams {

@@ -46,7 +46,7 @@ def _scheduler_context(units):
     return _route_ctx[units]
 
 
-@pytest.fixture(params=["auto", "tasks2", "tasks16"])
+@pytest.fixture(params=["auto", "tasks2", "tasks128"])
 def route(request):
     if request.param == "auto":
         yield request.param

@@ -131,8 +131,8 @@ def test_more_queries_than_resident_ctas():
                                  dict(N=45, C=20, loss="huber_loss", ratio=None, levels=[(8, 20), (0, 8)])])
 def test_cluster_sizes_match_oracle_and_each_other(cfg):
     """The result does not depend on how many CTAs share a query, or on whether they are a cluster or
-    workers of the task scheduler: the reduction order is fixed (16 point ranges, pairwise tree), so
-    records are bit-identical for cluster sizes 1..16 and for the scheduler (cluster_size=0)."""
+    workers of the task scheduler: the reduction order is fixed (128 point ranges, pairwise tree), so
+    records are bit-identical for cluster sizes 1..16 and for the scheduler with 1..128 tasks per evaluation."""
     sc = synth().make_scene(61, N=cfg["N"], C=cfg["C"], Hf=16, Wf=16, im_width=128, im_height=128,
                             K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
                             outlier_frac=0.1)
@@ -145,8 +145,8 @@ def test_cluster_sizes_match_oracle_and_each_other(cfg):
         g = fm().default_context().last_geometry
         if S:
             assert g["cluster_size"] == S and g["grid"] == S and g["tasks_per_evaluation"] == 0, g
-        else:  # automatic: a single query goes to one cluster (16 CTAs, or 8 with the whole shared memory each)
-            assert g["cluster_size"] in (8, 16) and g["grid"] == g["cluster_size"] and g["tasks_per_evaluation"] == 0, g
+        else:  # automatic: the task scheduler, as many tasks as keep >= 32 points each
+            assert g["cluster_size"] == 1 and g["tasks_per_evaluation"] >= 1 and g["grid"] == g["tasks_per_evaluation"], g
         compare("cluster=%d" % S, out["results"][0], out["history"], o, use_ratio=cfg["ratio"] is not None)
         if first is None:
             first = out
@@ -155,7 +155,8 @@ def test_cluster_sizes_match_oracle_and_each_other(cfg):
             for k in ("costs", "Rs", "ts", "points2d", "mask", "kept"):
                 assert np.array_equal(out["history"][k], first["history"][k], equal_nan=k in ("costs", "Rs", "ts")), k
     # the task scheduler with 1..16 tasks per evaluation (FMPNP_UNITS is read when a context is created)
-    for U in (1, 2, 4, 8, 16):
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    for U in (1, 2, 4, 8, 16, 32, 64, 128):
         os.environ["FMPNP_UNITS"] = str(U)
         try:
             ctx = fm().Context()
@@ -164,7 +165,7 @@ def test_cluster_sizes_match_oracle_and_each_other(cfg):
         out = fm().refine_batch([p, p, p], 6, loss=cfg["loss"], lambda_=0.01, ratio_threshold=cfg["ratio"],
                                 levels=cfg["levels"], track=True, ctx=ctx)
         g = ctx.last_geometry
-        assert g["cluster_size"] == 1 and g["tasks_per_evaluation"] == U and g["grid"] == 3 * U, g
+        assert g["cluster_size"] == 1 and g["tasks_per_evaluation"] == U and g["grid"] == min(3 * U, 2 * sms), g
         ctx.close()
         for i in range(3):
             assert same_records(out["results"][i], first["results"][0]), "units=%d differs from cluster=1" % U
@@ -174,7 +175,7 @@ def test_cluster_sizes_match_oracle_and_each_other(cfg):
 
 
 def test_automatic_geometry_and_batch_size_independence():
-    """Auto geometry (task scheduler): many tasks per evaluation for small batches, one for large ones;
+    """Auto geometry (task scheduler for every batch size): many tasks per evaluation for small batches, one for large ones;
     the records of a query are bit-identical whatever batch it is part of."""
     scs = [synth().make_scene(300 + i, N=500, C=1024, Hf=16, Wf=16, im_width=128, im_height=128,
                               K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
@@ -188,11 +189,8 @@ def test_automatic_geometry_and_batch_size_independence():
         r = fm().refine_batch(batch, 5, loss="geman_mcclure_loss", lambda_=0.01)["results"]
         g = ctx.last_geometry
         U = g["tasks_per_evaluation"]
-        if B * 32 <= sms:  # a handful of queries: one cluster each
-            assert g["cluster_size"] in (8, 16) and U == 0 and g["grid"] == g["cluster_size"] * B, g
-        else:
-            assert g["cluster_size"] == 1 and U in (1, 2, 4, 8, 16) and g["grid"] <= min(2 * sms, B * U), g
-            assert U == 16 or B * U >= 6 * sms, g   # about three tasks per CTA slot, at most 16 per evaluation
+        assert g["cluster_size"] == 1 and U in (1, 2, 4, 8) and g["grid"] <= min(2 * sms, B * U), g
+        assert U >= 4 or B * U >= 6 * sms, g   # about three tasks per CTA slot; a task keeps >= 64 of the 500 points
         if B >= 6 * sms:
             assert U == 1
         if B == 1:

@@ -49,7 +49,7 @@ def check_against(name, res, hist, exp, use_ratio, b=0):
 
 
 @pytest.mark.parametrize("solver,route", [("cholesky", "auto"), ("lu", "auto"), ("cholesky", "tasks2"),
-                                          ("cholesky", "tasks16")], indirect=["route"])
+                                          ("cholesky", "tasks128")], indirect=["route"])
 @pytest.mark.parametrize("name", golden_names())
 def test_c_abi_matches_reference_fixture(name, solver, route):
     fm = _fm()

@@ -3,7 +3,7 @@
 Every case draws N, C, map size, loss, damping, ratio threshold and (sometimes) a channel pyramid, builds a
 ragged batch of six such queries (B > 4: the task scheduler, with whatever number of tasks per evaluation the
 library picks), and checks each query against the oracle: pixel indices and masks bit-exact, costs and poses to
-the tight float64 bar.  The first query of the batch is then refined alone (B = 1: a thread-block cluster) and
+the tight float64 bar.  The first query of the batch is then refined alone by a thread-block cluster of 8 CTAs and
 must give the same record bit for bit."""
 import numpy as np
 import pytest
@@ -40,12 +40,12 @@ def test_random_ragged_batches(seed):
     kw = dict(loss=cfg["loss"], lambda_=cfg["lambda_"], ratio_threshold=cfg["ratio"], levels=cfg["levels"], track=True)
     out = fm().refine_batch(probs, cfg["n_iters"], **kw)
     g = fm().default_context().last_geometry
-    assert g["tasks_per_evaluation"] == 16 and g["cluster_size"] == 1, g  # six queries: 16 tasks per evaluation
+    assert g["tasks_per_evaluation"] >= 1 and g["cluster_size"] == 1, g  # six queries: the task scheduler
     for i, sc in enumerate(scs):
         o = run_oracle(sc, cfg["n_iters"], cfg["loss"], cfg["lambda_"], cfg["ratio"], cfg["levels"])
         compare("seed %d query %d %r" % (seed, i, cfg), out["results"][i], out["history"], o, b=i,
                 use_ratio=cfg["ratio"] is not None)
-    one = fm().refine_batch(probs[:1], cfg["n_iters"], **kw)
+    one = fm().refine_batch(probs[:1], cfg["n_iters"], cluster_size=8, **kw)
     assert fm().default_context().last_geometry["tasks_per_evaluation"] == 0
     assert same_records(one["results"][0], out["results"][0]), "cluster route differs from scheduler route: %r" % (cfg,)
     n = int(one["history"]["len"][0])
