@@ -22,7 +22,7 @@
 //                   into channel chunks.  One 48-byte record per point;
 //   all threads     apply the robust loss / ratio test, contract (S, b) with the 2x6
 //                   projection Jacobian and reduce the 6x6 normal equations in a fixed order
-//                   (16 point ranges, pairwise tree: the same bits for any launch geometry);
+//                   (128 point ranges, pairwise tree: the same bits for any launch geometry);
 //   warp 0          solves the damped system (warp-level Cholesky, pivoted-LU fallback),
 //                   applies the se(3) update and runs the accept / reject / damping schedule.
 // The trial evaluation of iteration i doubles as the linearisation of iteration i+1 when the
@@ -1121,15 +1121,17 @@ __global__ void __launch_bounds__(kThreads, 2) find_inliers_kernel(const LaunchP
 
 // ---------------------------------------------------------------------------------------------
 // Task scheduler (LaunchParams::scheduler == 1).
-// One evaluation of a query = `units` tasks, each a contiguous run of the 16 fixed point ranges.  Tasks sit
-// in one global FIFO (ticket queue: a consumer takes a ticket and waits for that position to be filled).
-// The CTA that completes the last task of an evaluation reduces ALL the per-point records of the query
-// (same fixed-order tree as above: bit-identical to the one-CTA-per-query path), runs the solve / accept /
-// reject step on the query's state (kept in global memory between evaluations) and queues the tasks of the
-// next evaluation.  Any number of queries keeps every CTA busy: no waves, no tail, no idle slots.
+// One evaluation of a query = `units` tasks (1..128), each an aligned run of the 128 fixed point ranges.  Tasks
+// sit in one global FIFO (ticket queue: a consumer takes a ticket and waits for that position to be filled).
+// A task streams its points and sums its own ranges (28 + 2 partials in global memory); the CTA that completes
+// the last task of an evaluation adds the partials along the same fixed pairwise tree (bit-identical to the
+// one-CTA-per-query path), runs the solve / accept / reject step on the query's state (kept in global memory
+// between evaluations) and queues the tasks of the next evaluation.  With a ratio test an evaluation takes two
+// rounds of tasks (max |rho| first, sums second).  Any number of queries keeps every CTA busy: no waves, no
+// tail, no idle slots; a single query is spread over up to 128 CTAs.
 // ---------------------------------------------------------------------------------------------
 constexpr unsigned long long kQueueEmpty = ~0ull;
-constexpr int kPartStride = 32;  // doubles per task partial: 28 sums, 2 counts (as int64), 2 unused
+constexpr int kPartStride = 32;  // doubles per task partial: 28 sums, 2 counts (as int64), max |rho|, NaN flag (int64)
 constexpr unsigned long long kWaitLimitNs = 20ull * 1000 * 1000 * 1000;  // then the kernel gives up instead of hanging
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
