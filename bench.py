@@ -347,6 +347,32 @@ def main():
                 "peak_note": "peak is the measured COPY bandwidth (half reads, half writes); this kernel only reads, "
                              "so frac can exceed 1 - see dram__cycles_active in profiles/ for the remaining headroom"}
 
+    # context for the fraction: what plain library kernels stream on THIS GPU right now (not the contract's peak)
+    try:
+        free_b, _ = torch.cuda.mem_get_info(dev)
+        n_el = int(min(4 << 30, free_b // 3) // 4)
+        xs = torch.empty(n_el, dtype=torch.float32, device=dev).fill_(1.0)
+        ys = torch.empty(n_el // 2, dtype=torch.float32, device=dev)
+
+        def best_ms(fn, reps=4):
+            fn()
+            torch.cuda.synchronize()
+            best = 1e30
+            for _ in range(reps):
+                a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a_.record()
+                fn()
+                b_.record()
+                torch.cuda.synchronize()
+                best = min(best, a_.elapsed_time(b_))
+            return best
+        roofline["context"] = {"torch_sum_read_gbs": n_el * 4 / best_ms(lambda: xs.sum()) / 1e6,
+                               "torch_copy_gbs": 2 * (n_el // 2) * 4 / best_ms(lambda: ys.copy_(xs[: n_el // 2])) / 1e6,
+                               "note": "library kernels on this GPU in this run (16 GB streaming read, 8+8 GB copy)"}
+        del xs, ys
+    except Exception as e:
+        roofline["context"] = {"error": repr(e)}
+
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": dict(cfg, sort_points=bool(args.sort_points), outlier_frac=outl), "roofline": roofline, "clocks": clk.summary(),
@@ -455,6 +481,40 @@ def main():
                                    "note": "feature_pnp level: query + reference hypercolumns (CHW fp32) and points in pinned "
                                            "host memory -> H2D -> fmpnp_sobel_pack + fmpnp_gather_descriptors -> refinement "
                                            "-> D2H; rank-local, not aggregated"}
+            # ---- the pipeline call itself: hypercolumns already on the GPU (where the CNN leaves them), one
+            # query per call as s2dhm does: build_problem (Sobel + pack + descriptor gather) -> refinement -> pose
+            if levels is None:
+                import collections
+                import model as dropin
+                from helpers import utils as hu
+                from pose_prediction import optimize_feature_pnp as adapter
+                Pred = collections.namedtuple("Pred", "points_3d reference_inliers matrix")
+                preds = []
+                for i in range(min(8, A)):
+                    P = scenes[i].pts3D.cpu()
+                    u = (scenes[i].K[0, 0] * P[:, 0] / P[:, 2] + scenes[i].K[0, 2]).clamp(0, 1023)
+                    v = (scenes[i].K[1, 1] * P[:, 1] / P[:, 2] + scenes[i].K[1, 2]).clamp(0, 1023)
+                    T = np.eye(4)
+                    T[:3, :3], T[:3, 3] = scenes[i].R0.numpy(), scenes[i].t0.numpy()
+                    preds.append(Pred(P.numpy(), torch.stack([u, v], 1).numpy(), T))
+                mdl = dropin.sparseFeaturePnP(n_iters=cfg["n_iters"], loss_fn=getattr(hu, cfg["loss"]),
+                                              lambda_=cfg["lambda_"], ratio_threshold=cfg["ratio_threshold"])
+
+                def pipeline_query(i):
+                    prob = adapter.build_problem(qh_dev[i], rh_dev[i], preds[i], scenes[i].K, [1024, 1024])
+                    return mdl.forward_packed(prob)
+
+                pipeline_query(0)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for i in range(len(preds)):
+                    pipeline_query(i)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                line["pipeline_call"] = {"ms_per_query": 1e3 * dt / len(preds), "queries": len(preds),
+                                         "note": "one query per call, hypercolumns resident on the GPU: build_problem "
+                                                 "(fmpnp_sobel_pack + fmpnp_gather_descriptors) -> forward_packed -> "
+                                                 "CPU float64 pose; wall clock"}
             del qh_host, qh_dev, rh_dev
 
     # ---- e2e at the reference's own Python call: sparseFeaturePnP.forward, one query per call, CPU float64 CHW
