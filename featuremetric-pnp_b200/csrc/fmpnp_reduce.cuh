@@ -1,0 +1,243 @@
+// fmpnp_reduce.cuh -- the per-point phase of a pose evaluation (robust loss, ratio test, contraction with the projection Jacobian) and the fixed-order reductions of the normal equations.
+// Part of the refinement kernels (fmpnp_kernels.cu); not a public interface.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "fmpnp_stream.cuh"
+
+namespace fmpnp {
+
+namespace cg = cooperative_groups;
+
+// ---------------------------------------------------------------------------------------------
+// Deterministic reductions.  The points of a query are cut into kRanges = 128 fixed ranges (the same
+// for every launch geometry).  A range is summed by ONE warp in a fixed order (lanes stride the range,
+// then a transposition through the warp's idle slice of the staging ring and a pairwise tree over the
+// 32 lanes); range totals are added pairwise along the aligned binary tree over the range index: first
+// over the consecutive ranges a warp owns, then over the warps of the CTA, then over the CTAs of the
+// cluster or the tasks of the evaluation.  Every owner holds an aligned power-of-two run of ranges, so
+// the result is bit-identical for every cluster size, task count, batch size and ring geometry.
+// ---------------------------------------------------------------------------------------------
+// (kLaneStride, kWarpScratchDoubles: fmpnp_kernels.cuh -- the host sizes the ring so that a warp's slice holds them)
+
+// Combines the per-CTA values every CTA of the cluster left in its own Shared::cpart[par] /
+// cpart_i[par]: all CTAs read all partials through distributed shared memory and add them in
+// the same pairwise order, so every CTA ends up with bit-identical totals (and then takes the
+// same LM decisions).  One hardware cluster barrier per reduction; the two halves of cpart
+// alternate, so a half is only rewritten after the next barrier, when every CTA has read it.
+template <bool MAX>
+__device__ __forceinline__ void cluster_combine(Shared& sh, int csize, int32_t& par, int nv, double* out, int ni,
+                                                int32_t* iout) {
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    const int tid = threadIdx.x;
+    if (tid < nv) {
+        double v[kMaxCluster];
+#pragma unroll
+        for (int r = 0; r < kMaxCluster; ++r) v[r] = r < csize ? *cl.map_shared_rank(&sh.cpart[par][tid], r) : 0.0;
+#pragma unroll
+        for (int w = 1; w < kMaxCluster; w <<= 1) {
+            if (w < csize) {
+#pragma unroll
+                for (int i = 0; i + w < kMaxCluster; i += 2 * w) v[i] = MAX ? fmax(v[i], v[i + w]) : __dadd_rn(v[i], v[i + w]);
+            }
+        }
+        out[tid] = v[0];
+    } else if (tid >= 32 && tid < 32 + ni) {
+        const int k = tid - 32;
+        int32_t s = 0;
+        for (int r = 0; r < csize; ++r) {
+            const int32_t x = *cl.map_shared_rank(&sh.cpart_i[par][k], r);
+            s = MAX ? (s | x) : (s + x);
+        }
+        iout[k] = s;
+    }
+    par ^= 1;
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-point phase: robust loss, ratio test, contraction with the projection Jacobian, sums.
+// Leaves sh.ev[0..27], sh.ev_count (survivors), sh.ev_nsup (supported) and sh.ev_cost (mean rho).
+// ---------------------------------------------------------------------------------------------
+// max |rho| over the supported points [c.n0, c.n1) of this CTA and whether any is NaN (torch.max propagates NaN):
+// the ingredients of ratio_threshold_feature_errors' limit (model.py:120-129).  Valid in thread 0 after the call.
+__device__ __forceinline__ void block_ratio_max(const EvalCtx& c, Shared& sh, double& mm, int& nf) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    double m = -INFINITY;
+    int nanf = 0;
+    for (int n = c.n0 + tid; n < c.n1; n += kThreads) {
+        if (!__ldcg(c.supp + n)) continue;  // .cg: records may have been written by another CTA (task scheduler)
+        const double x = __dmul_rn(0.5, __ldcg(c.rec + (size_t)n * kRecDoubles));
+        double rho = x, w = 1.0;
+        if (c.ratio_mode == 1) robust_loss(c.loss_id, c.alpha, x, rho, w);
+        const double a = fabs(rho);
+        if (a != a) nanf = 1;
+        m = fmax(m, a);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        m = fmax(m, shfl_xor_f64(m, off));
+        nanf |= __shfl_xor_sync(0xffffffffu, nanf, off);
+    }
+    if (lane == 0) {
+        sh.red[warp][0] = m;
+        sh.red_i[warp][0] = nanf;
+    }
+    __syncthreads();
+    mm = -INFINITY;
+    nf = 0;
+    if (tid == 0) {
+        mm = sh.red[0][0];
+        nf = sh.red_i[0][0];
+        for (int w = 1; w < kWarps; ++w) {
+            mm = fmax(mm, sh.red[w][0]);
+            nf |= sh.red_i[w][0];
+        }
+    }
+}
+
+template <bool GRAD>
+__device__ void reduce_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+    const QueryDev& q = *c.q;
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const bool use_ratio = c.ratio_mode != 0;
+
+    if (use_ratio && !c.limit_given) {
+        double mm;
+        int nf;
+        block_ratio_max(c, sh, mm, nf);
+        if (tid == 0) {
+            if (c.csize > 1) {
+                sh.cpart[rp.cpar][0] = mm;
+                sh.cpart_i[rp.cpar][0] = nf;
+            } else {
+                sh.limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
+            }
+        }
+        if (c.csize > 1) {
+            cluster_combine<true>(sh, c.csize, rp.cpar, 1, &sh.climit, 1, &sh.climit_nan);
+            if (tid == 0) sh.limit = sh.climit_nan ? NAN : __dmul_rn(sh.climit, c.thr);
+        }
+        __syncthreads();
+    }
+    const double limit = use_ratio ? sh.limit : 0.0;
+
+    const double fx = q.K[0], fy = q.K[4];
+    const int per = c.range_len;              // points per fixed range
+    const int nr = kRanges / c.csize;         // ranges this CTA owns: an aligned power-of-two run
+    const int r_first = c.crank * nr;
+    const int rpw = nr >= kWarps ? nr / kWarps : 1;  // consecutive ranges per warp ...
+    const int wact = nr >= kWarps ? kWarps : nr;     // ... of the warps that own any
+    double* const wscr = reinterpret_cast<double*>(c.ring + (size_t)warp * c.ring_per_warp);  // idle ring slice
+    double* const stack = wscr + 28 * kLaneStride;
+    int32_t cnt[2] = {0, 0};  // survivors, supported (this lane, all its ranges)
+    if (warp < wact) {
+        for (int rr = 0; rr < rpw; ++rr) {
+            const int r0 = min(q.N, (r_first + warp * rpw + rr) * per), r1 = min(q.N, r0 + per);
+            double acc[28];
+#pragma unroll
+            for (int i = 0; i < 28; ++i) acc[i] = 0.0;
+            for (int n = r0 + lane; n < r1; n += 32) {
+                const bool sup = __ldcg(c.supp + n) != 0;
+                bool keep = false;
+                if (sup) {
+                    ++cnt[1];
+                    const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+                    const double2 rc0 = __ldcg(r);
+                    const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
+                    double rho = x, w = 1.0;
+                    if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
+                    keep = !use_ratio || (fabs(rho) < limit);
+                    if (keep) {
+                        ++cnt[0];
+                        acc[27] = __dadd_rn(acc[27], rho);
+                        if (GRAD) {
+                            const double2 rc1 = __ldcg(r + 1), rc2 = __ldcg(r + 2);
+                            const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
+                                                          q.im_w, q.im_h);
+                            contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
+                        }
+                    }
+                }
+                if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
+                if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
+            }
+            // the 32 lane partials of each of the 28 sums -> lane i (transposition), pairwise tree over the lanes
+            __syncwarp();  // the rows of the previous range have been read
+#pragma unroll
+            for (int i = 0; i < 28; ++i) wscr[i * kLaneStride + lane] = acc[i];
+            __syncwarp();
+            if (lane < 28) {
+                const double* row = wscr + lane * kLaneStride;
+                double x[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) x[k] = __dadd_rn(row[2 * k], row[2 * k + 1]);
+#pragma unroll
+                for (int w = 1; w < 16; w <<= 1) {
+#pragma unroll
+                    for (int k = 0; k + w < 16; k += 2 * w) x[k] = __dadd_rn(x[k], x[k + w]);
+                }
+                double tot = x[0];
+                int level = 0;
+                for (int kk = rr; kk & 1; kk >>= 1) {  // binary-counter stack: pairwise tree over this warp's ranges
+                    tot = __dadd_rn(stack[level * 28 + lane], tot);
+                    ++level;
+                }
+                stack[level * 28 + lane] = tot;
+                if (rr == rpw - 1) sh.wtot[warp][lane] = tot;  // rpw is a power of two: the total is on top
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) cnt[i] += __shfl_xor_sync(0xffffffffu, cnt[i], off);
+    }
+    if (lane == 0) {
+        sh.red_i[warp][0] = cnt[0];
+        sh.red_i[warp][1] = cnt[1];
+    }
+    __syncthreads();
+    int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
+    if (tid < 28) {  // pairwise tree over the warps that own ranges
+        double v[kWarps];
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) v[w] = w < wact ? sh.wtot[w][tid] : 0.0;
+#pragma unroll
+        for (int w = 1; w < kWarps; w <<= 1) {
+            if (w < wact) {
+#pragma unroll
+                for (int k = 0; k + w < kWarps; k += 2 * w) v[k] = __dadd_rn(v[k], v[k + w]);
+            }
+        }
+        if (c.part_out)
+            c.part_out[tid] = v[0];
+        else if (c.csize > 1)
+            sh.cpart[rp.cpar][tid] = v[0];
+        else
+            sh.ev[tid] = v[0];
+    } else if (tid >= 32 && tid < 34) {
+        int32_t tot_i = 0;
+        for (int w = 0; w < kWarps; ++w) tot_i += sh.red_i[w][tid - 32];
+        if (c.part_out)
+            reinterpret_cast<long long*>(c.part_out)[28 + (tid - 32)] = tot_i;
+        else if (c.csize > 1)
+            sh.cpart_i[rp.cpar][tid - 32] = tot_i;
+        else
+            iout[tid - 32] = tot_i;
+    }
+    if (c.part_out) {  // the CTA that completes the evaluation combines the tasks' partials (combine_parts)
+        __syncthreads();
+        return;
+    }
+    if (c.csize > 1)
+        cluster_combine<false>(sh, c.csize, rp.cpar, 28, sh.ev, 2, iout);
+    else
+        __syncthreads();
+    if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;  // mean; 0/0 = NaN like torch's empty mean
+    __syncthreads();
+}
+
+}  // namespace fmpnp
