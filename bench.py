@@ -54,6 +54,9 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-adapter-e2e", action="store_true")
     ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
+    ap.add_argument("--skew-maps", type=int, default=0,
+                    help="experiment: place F, Gx, Gy of a query in one buffer, Gx / Gy displaced by this many extra rows "
+                         "(0 = three separate allocations, as the product's callers have them)")
     ap.add_argument("--sort-points", action="store_true",
                     help="experiment: order each query's points by feature-map cell (DRAM page / TLB locality)")
     ap.add_argument("--outliers", type=float, default=None, help="outlier fraction (default: 0 for cfg2, 0.1 otherwise)")
@@ -261,6 +264,15 @@ def main():
     outl = args.outliers if args.outliers is not None else (0.0 if args.config == "gn_inlier" else 0.1)
     scenes = [synth.make_scene(rank * B + q, N=args.points, C=args.channels, Hf=args.map, Wf=args.map, device=dev,
                                outlier_frac=outl) for q in range(B)]
+    if args.skew_maps:
+        for sc in scenes:
+            n, rowlen = sc.F.numel(), sc.F.shape[-1]
+            buf = torch.empty(3 * n + 3 * args.skew_maps * rowlen, dtype=torch.float32, device=dev)
+            o1, o2 = n + args.skew_maps * rowlen, 2 * n + 3 * args.skew_maps * rowlen
+            for name, off in (("F", 0), ("Gx", o1), ("Gy", o2)):
+                v = buf[off:off + n].view(getattr(sc, name).shape)
+                v.copy_(getattr(sc, name))
+                setattr(sc, name, v)
     if args.sort_points:
         for sc in scenes:
             P = sc.pts3D.cpu()
