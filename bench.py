@@ -301,12 +301,23 @@ def main():
                         ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=res_dev)
         if i is not None:
             kev[i][1].record()
-        if world > 1:
-            return sharding.gather_result_records(res_dev, world * B)
+        if world > 1:  # the single exchange of the path: result records, on NCCL's own stream (no lock-step)
+            gathered, work = sharding.gather_result_records(res_dev, world * B, async_op=True)
+            pending.append(work)
+            return gathered
         return res_dev
+
+    pending = []
+
+    def drain():
+        for w in pending:
+            if w is not None:
+                w.wait()
+        del pending[:]
 
     for _ in range(max(args.warmup, 0)):
         step()
+    drain()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -316,6 +327,7 @@ def main():
         start.record()
         for i in range(args.steps):
             step(i)
+        drain()  # every step's gather has completed before the clock stops
         end.record()
         torch.cuda.synchronize()
         if world > 1:

@@ -19,14 +19,16 @@ def shard_range(n_queries, rank, world_size):
     return lo, hi
 
 
-def gather_result_records(local_records, n_queries, group=None):
+def gather_result_records(local_records, n_queries, group=None, async_op=False):
     """All-gathers per-rank result records.
 
     local_records: uint8 tensor [n_local, record_bytes] (device tensor under NCCL, CPU under gloo)
     holding this rank's block as laid out by shard_range.  Returns [n_queries, record_bytes] on
-    every rank, in global query order."""
+    every rank, in global query order.  With `async_op=True` returns (records, work): the collective runs
+    on the backend's own stream, so the caller's next kernels do not wait for the other ranks; call
+    `work.wait()` (if not None) before reading `records`."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
-        return local_records[:n_queries]
+        return (local_records[:n_queries], None) if async_op else local_records[:n_queries]
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     per = -(-n_queries // world)
@@ -37,8 +39,8 @@ def gather_result_records(local_records, n_queries, group=None):
     pad = torch.zeros((per, rec), dtype=torch.uint8, device=local_records.device)
     pad[: hi - lo] = local_records
     out = torch.empty((world * per, rec), dtype=torch.uint8, device=local_records.device)
-    dist.all_gather_into_tensor(out, pad, group=group)
-    return out[:n_queries]
+    work = dist.all_gather_into_tensor(out, pad, group=group, async_op=async_op)
+    return (out[:n_queries], work) if async_op else out[:n_queries]
 
 
 def records_to_numpy(records, dtype):
