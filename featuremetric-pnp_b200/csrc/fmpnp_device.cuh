@@ -292,6 +292,21 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
     return v;
 }
+// base + idx * pitch as ONE instruction (IMAD.WIDE.U32); written in PTX so that the compiler does not share the
+// product between rows and then pay two adds per row for the different bases
+__device__ __forceinline__ const char* row_address(const char* base, uint32_t idx, uint32_t pitch) {
+    unsigned long long r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(idx), "r"(pitch), "l"((unsigned long long)base));
+    return reinterpret_cast<const char*>(r);
+}
+__device__ __forceinline__ void sts64(uint32_t addr, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ double2 lds128d(uint32_t addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 // waits until at most `n` of this thread's commit groups are still pending (n is uniform)
 __device__ __forceinline__ void cp_async_wait_pending(int n) {

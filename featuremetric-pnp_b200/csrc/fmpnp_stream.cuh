@@ -311,11 +311,20 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
     auto copy_point = [&](int buf, int k, uint32_t off, int nv, uint32_t dst) {
         const uint32_t cell = (uint32_t)bcell[buf * 32 + k], n = (uint32_t)bn[buf * 32 + k];
         const char* s[4];
-        s[0] = baseF + (size_t)cell * pitch + off;
-        s[ROWS - 1] = baseR + (size_t)n * pitch + off;
-        if (GRAD) {
-            s[1] = baseGx + (size_t)cell * pitch + off;
-            s[2] = baseGy + (size_t)cell * pitch + off;
+        if (SHORT) {  // off == 0
+            s[0] = row_address(baseF, cell, pitch);
+            s[ROWS - 1] = row_address(baseR, n, pitch);
+            if (GRAD) {
+                s[1] = row_address(baseGx, cell, pitch);
+                s[2] = row_address(baseGy, cell, pitch);
+            }
+        } else {
+            s[0] = baseF + (size_t)cell * pitch + off;
+            s[ROWS - 1] = baseR + (size_t)n * pitch + off;
+            if (GRAD) {
+                s[1] = baseGx + (size_t)cell * pitch + off;
+                s[2] = baseGy + (size_t)cell * pitch + off;
+            }
         }
         dst += lane * 16;
         const int full = nv >> 5, tail = nv & 31;  // whole 512-byte warp copies, then a partial one
@@ -385,6 +394,37 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
             if (act && sl + L < nvec) {
                 const uint32_t p2 = p + L * 16;
                 acc4<GRAD>(p2, p2 + rowB, p2 + 2 * rowB, p2 + (ROWS - 1) * rowB, a);
+            }
+            if (GRAD && (LOG2L == 3 || LOG2L == 4)) {
+                // Sum over the L lanes of a point through the slot that has just been consumed: every lane stores
+                // its six partials, then one lane per (point, value) adds the L of them in the order of the
+                // butterfly (pairs at distance L/2, L/4, ...).  45 instructions instead of 80 for the shuffles,
+                // selects and register moves of the butterfly.
+                constexpr int STR = L + 2;  // doubles per (point, value) row: 16-byte aligned, spreads the banks
+                __syncwarp();               // every lane has read its pieces of the slot
+                const uint32_t wbase = src0 + (uint32_t)((sg * 6) * STR + sl) * 8u;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) sts64(wbase + (uint32_t)(j * STR) * 8u, a[j]);
+                __syncwarp();
+                if (lane < 6 * G) {
+                    const int g = lane / 6, j = lane - g * 6, kk = it * G + g;
+                    const uint32_t rbase = src0 + (uint32_t)(lane * STR) * 8u;
+                    double x[L];
+#pragma unroll
+                    for (int i = 0; i < L / 2; ++i) {
+                        const double2 v = lds128d(rbase + (uint32_t)i * 16u);
+                        x[2 * i] = v.x;
+                        x[2 * i + 1] = v.y;
+                    }
+#pragma unroll
+                    for (int w = L / 2; w >= 1; w >>= 1) {
+#pragma unroll
+                        for (int i = 0; i < w; ++i) x[i] = __dadd_rn(x[i], x[i + w]);
+                    }
+                    if (kk < cnt) c.rec[(size_t)bn[buf * 32 + kk] * kRecDoubles + j] = x[0];
+                }
+                __syncwarp();  // every lane is done with the slot: it may be refilled
+                return;
             }
             double* rec_n = c.rec + (size_t)bn[buf * 32 + (act ? k : 0)] * kRecDoubles;
             if (GRAD) {

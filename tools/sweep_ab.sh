@@ -18,12 +18,8 @@ for l in sys.stdin:
   done
   unset FMPNP_LIB
 }
-one --queries 256
-one --config geman_lm --queries 256
-one --config pyramid --points 8192 --queries 256
 one --config geman_lm --points 8192 --channels 128 --queries 296
-one --config geman_lm --points 8192 --channels 256 --queries 296
-one --config geman_lm --points 8192 --channels 384 --queries 296
-one --config geman_lm --points 8192 --channels 512 --queries 296
-one --config geman_lm --queries 8
+one --config geman_lm --points 8192 --channels 64 --queries 296
+one --config pyramid --points 8192 --queries 256
+one --queries 256
 cat $out
