@@ -38,6 +38,7 @@ struct fmpnp_ctx {
     int ctas_per_sm = 0;
     int cluster = 0;
     int scheduler = 1;   // 1: task queue (default), 0: one CTA / cluster per query
+    int watchdog_s = 20;   // FMPNP_WATCHDOG_S: seconds a CTA may wait for a task before the launch is abandoned (0 = off)
     int small_batch_clusters = 0;  // 1: a handful of queries (B <= 4) go to clusters even with the scheduler on
     int units = 0;       // tasks per evaluation (0 = automatic)
     QueryState* d_states = nullptr;
@@ -296,6 +297,7 @@ int prepare_tasks(fmpnp_ctx* ctx, int32_t B, const Geometry& g, LaunchParams& lp
     lp.sched.done = ctx->d_sched + 2;
     lp.sched.error = ctx->d_sched + 3;
     lp.sched.started = ctx->d_sched + 4;
+    lp.sched.wait_limit_ns = (unsigned long long)ctx->watchdog_s * 1000000000ull;
     lp.sched.cap = ctx->cap_queue;
     lp.sched.units = g.units;
     lp.sched.states = ctx->d_states;
@@ -343,6 +345,8 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     ctx->scheduler = env_int("FMPNP_SCHEDULER", 1);
     ctx->units = env_int("FMPNP_UNITS", 0);
     ctx->small_batch_clusters = env_int("FMPNP_SMALL_BATCH_CLUSTERS", 0);
+    ctx->watchdog_s = env_int("FMPNP_WATCHDOG_S", 20);
+    if (ctx->watchdog_s < 0) ctx->watchdog_s = 0;
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     *out = ctx;
     return FMPNP_SUCCESS;

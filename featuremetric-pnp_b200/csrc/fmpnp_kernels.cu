@@ -254,7 +254,6 @@ __global__ void __launch_bounds__(kThreads, 2) find_inliers_kernel(const LaunchP
 // ---------------------------------------------------------------------------------------------
 constexpr unsigned long long kQueueEmpty = ~0ull;
 constexpr int kPartStride = 32;  // doubles per task partial: 28 sums, 2 counts (as int64), max |rho|, NaN flag (int64)
-constexpr unsigned long long kWaitLimitNs = 20ull * 1000 * 1000 * 1000;  // then the kernel gives up instead of hanging
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
     unsigned long long t;
@@ -295,7 +294,7 @@ __device__ __forceinline__ int dequeue_task(const SchedDev& s, int B) {
         if ((spin & 1023u) == 1023u) {
             const unsigned long long now = global_timer_ns();
             if (t0 == 0) t0 = now;
-            if (now - t0 > kWaitLimitNs) {
+            if (s.wait_limit_ns != 0 && now - t0 > s.wait_limit_ns) {  // give up instead of hanging
                 atomicExch(s.error, 1u);
                 return -1;
             }

@@ -73,6 +73,7 @@ struct SchedDev {
     unsigned int* done;         // finished queries
     unsigned int* error;        // watchdog / protocol error flag
     unsigned int* started;      // queries whose first evaluation has been queued
+    unsigned long long wait_limit_ns;  // a CTA that waits this long for a task raises `error` (0 = wait forever)
     uint32_t cap;               // power of two
     int32_t units;              // tasks per evaluation: a power of two, 1..128
     QueryState* states;         // [B]
