@@ -89,10 +89,11 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.part_out = nullptr;
         c.limit_given = false;
         {
-            const int per = max(1, (q.N + kRanges - 1) / kRanges);
+            c.nranges = ranges_of(q.N);
+            const int per = max(1, (q.N + c.nranges - 1) / c.nranges);
             c.range_len = per;
-            c.n0 = min(q.N, crank * (kRanges / csize) * per);
-            c.n1 = min(q.N, (crank + 1) * (kRanges / csize) * per);
+            c.n0 = min(q.N, crank * (c.nranges / csize) * per);
+            c.n1 = min(q.N, (crank + 1) * (c.nranges / csize) * per);
         }
         c.h_px = nullptr;
         c.h_mask = nullptr;
@@ -269,10 +270,10 @@ __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) {
 }
 
 // thread 0 only: queues the `units` tasks of query q's next evaluation (its state is already in global memory)
-__device__ __forceinline__ void enqueue_evaluation(const SchedDev& s, int q) {
+__device__ __forceinline__ void enqueue_evaluation(const SchedDev& s, int q, int units) {
     __threadfence();  // state (and, for the finisher, everything before) visible before the tasks are
-    const unsigned int base = atomicAdd(s.tail, (unsigned int)s.units);
-    for (int u = 0; u < s.units; ++u) {
+    const unsigned int base = atomicAdd(s.tail, (unsigned int)units);
+    for (int u = 0; u < units; ++u) {
         const unsigned int pos = base + (unsigned int)u;
         const unsigned long long v = ((unsigned long long)pos << 32) | (unsigned int)(q * kRanges + u + 1);
         *reinterpret_cast<volatile unsigned long long*>(&s.queue[pos & (s.cap - 1)]) = v;
@@ -437,6 +438,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
     auto start_query = [&](int q) {
         const QueryDev& qd = p.queries[q];
         QueryState& g = sc.states[q];
+        const int uq = min(sc.units, ranges_of(qd.N));  // tasks per evaluation of THIS query
         for (int i = 0; i < 9; ++i) g.R[i] = g.Rn[i] = g.Rb[i] = qd.R0[i];
         for (int i = 0; i < 3; ++i) g.t[i] = g.tn[i] = g.tb[i] = qd.t0[i];
         for (int i = 0; i < 27; ++i) g.lin[i] = 0.0;
@@ -457,14 +459,14 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         g.it = 0;
         if (MODE == kModeRefine) p.results[q].status = FMPNP_STATUS_INCOMPLETE;
         if (MODE == kModeComputeCost)
-            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, uq);
         else if (MODE == kModeFindInliers)
-            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, sc.units);
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, uq);
         else if (p.n_levels > 0)  // multilevel: compute_cost on ALL channels first (model.py:182)
-            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, sc.units);
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, uq);
         else
-            describe_evaluation(g, qd.R0, qd.t0, kPhaseFirst, 1, 0, qd.C, p.use_ratio ? 1 : 0, p.loss_id, 0, sc.units);
-        enqueue_evaluation(sc, q);
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseFirst, 1, 0, qd.C, p.use_ratio ? 1 : 0, p.loss_id, 0, uq);
+        enqueue_evaluation(sc, q, uq);
     };
 
     for (;;) {
@@ -483,6 +485,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         const QueryDev& q = p.queries[qi];
         QueryState& g = sc.states[qi];
         const volatile QueryState& gv = g;
+        const int uq = min(sc.units, ranges_of(q.N));  // tasks per evaluation of this query
         if (tid < 9) evpose[tid] = gv.evR[tid];
         if (tid >= 9 && tid < 12) evpose[tid] = gv.evt[tid - 9];
 
@@ -512,8 +515,9 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.h_kept = nullptr;
         if (hist_entry >= 0) hist_slices(p, qi, hist_entry, c);
         {
-            const int per = max(1, (q.N + kRanges - 1) / kRanges);
-            const int rpu = kRanges / sc.units;  // fixed ranges per task
+            c.nranges = ranges_of(q.N);
+            const int per = max(1, (q.N + c.nranges - 1) / c.nranges);
+            const int rpu = c.nranges / uq;  // fixed ranges per task
             c.range_len = per;
             c.n0 = min(q.N, u * rpu * per);
             c.n1 = min(q.N, (u + 1) * rpu * per);
@@ -526,7 +530,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         // round 0 only leaves the task's max |rho|, the CTA that completes the round publishes the limit and
         // queues the tasks again (round 1: sums only, the records come from L2).
         const int round = gv.ev_round;
-        const bool multi = sc.units > 1, ratio = c.ratio_mode != 0;
+        const bool multi = uq > 1, ratio = c.ratio_mode != 0;
         double* const parts = sc.part + (size_t)qi * sc.units * kPartStride;
         if (round == 0) {
             rp.pos = 0;
@@ -552,7 +556,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
                 if (tid == 0) sh.limit = gv.ev_limit;
                 __syncthreads();
             }
-            c.csize = sc.units;
+            c.csize = uq;
             c.crank = u;
             c.part_out = parts + u * kPartStride;
             c.limit_given = ratio;
@@ -577,14 +581,14 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             if (tid == 0) {
                 double mm = -INFINITY;
                 long long nf = 0;
-                for (int r = 0; r < sc.units; ++r) {
+                for (int r = 0; r < uq; ++r) {
                     mm = fmax(mm, __ldcg(parts + r * kPartStride + 30));
                     nf |= __ldcg(reinterpret_cast<const long long*>(parts) + r * kPartStride + 31);
                 }
                 g.ev_limit = nf ? NAN : __dmul_rn(mm, c.thr);  // torch.max propagates NaN
                 g.ev_round = 1;
-                g.pending = sc.units;
-                enqueue_evaluation(sc, qi);
+                g.pending = uq;
+                enqueue_evaluation(sc, qi, uq);
             }
             continue;
         }
@@ -595,7 +599,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         if (tid == 0) load_state(sh, gv);
         __syncthreads();
         if (multi)
-            combine_parts(sh, parts, sc.units);
+            combine_parts(sh, parts, uq);
         else if (grad)
             reduce_points<true>(c, evpose, evpose + 9, sh, rp);
         else
@@ -671,7 +675,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
                     const int c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
                     const int Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
                     describe_evaluation(g, sh.R, sh.t, kPhaseFirst, 1, c0, Cl, p.use_ratio ? 1 : 0, p.loss_id, sh.hist_len,
-                                        sc.units);
+                                        uq);
                 }
                 have_eval = true;
             } else if (next == kTryStep) {
@@ -689,7 +693,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
                 }
                 if (tid == 0)
                     describe_evaluation(g, sh.Rn, sh.tn, kPhaseTrial, 1, gv.ev_c0, gv.ev_Cl, p.use_ratio ? 1 : 0, p.loss_id,
-                                        sh.hist_len, sc.units);
+                                        sh.hist_len, uq);
                 have_eval = true;
             } else {  // kFinishLevel (model.py:491-494): best pose unless the loop was left on an empty support
                 if (tid == 0) {
@@ -712,7 +716,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
                 store_state(sh, g);
                 g.level = lvl;
                 g.it = it;
-                enqueue_evaluation(sc, qi);
+                enqueue_evaluation(sc, qi, uq);
             }
         }
     }

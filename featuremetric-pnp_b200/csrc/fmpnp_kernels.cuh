@@ -11,7 +11,8 @@ namespace fmpnp {
 constexpr int kWarps = 8;                         // each streams its own points through its slice of the ring
 constexpr int kThreads = kWarps * 32;             // 256
 constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
-constexpr int kRanges = 128;                      // fixed reduction ranges per query == max tasks per evaluation
+constexpr int kRanges = 128;                      // max fixed reduction ranges per query == max tasks per evaluation
+constexpr int kMinRanges = 16;                    // min (small queries) == max cluster size
 constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
 constexpr int kLaneStride = 33;                   // reduction scratch: doubles per transposed row (conflict-free columns)
 constexpr int kWarpScratchDoubles = 28 * kLaneStride + 8 * 28;  // per warp: transposition + pairwise-tree stack

@@ -10,8 +10,8 @@ namespace fmpnp {
 namespace cg = cooperative_groups;
 
 // ---------------------------------------------------------------------------------------------
-// Deterministic reductions.  The points of a query are cut into kRanges = 128 fixed ranges (the same
-// for every launch geometry).  A range is summed by ONE warp in a fixed order (lanes stride the range,
+// Deterministic reductions.  The points of a query are cut into ranges_of(N) = 16...128 fixed ranges (a function
+// of the query only, the same for every launch geometry).  A range is summed by ONE warp in a fixed order (lanes stride the range,
 // then a transposition through the warp's idle slice of the staging ring and a pairwise tree over the
 // 32 lanes); range totals are added pairwise along the aligned binary tree over the range index: first
 // over the consecutive ranges a warp owns, then over the warps of the CTA, then over the CTAs of the
@@ -126,7 +126,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
 
     const double fx = q.K[0], fy = q.K[4];
     const int per = c.range_len;              // points per fixed range
-    const int nr = kRanges / c.csize;         // ranges this CTA owns: an aligned power-of-two run
+    const int nr = c.nranges / c.csize;       // ranges this CTA owns: an aligned power-of-two run
     const int r_first = c.crank * nr;
     const int rpw = nr >= kWarps ? nr / kWarps : 1;  // consecutive ranges per warp ...
     const int wact = nr >= kWarps ? kWarps : nr;     // ... of the warps that own any

@@ -39,6 +39,14 @@ struct RingPos {
     int32_t cpar;  // which half of Shared::cpart the next cluster reduction uses
 };
 
+// Number of fixed reduction ranges of a query: a function of its point count only (never of the launch), a power
+// of two in [16, 128] such that a range holds about 32 points -- a full warp -- when the query has enough of them.
+__device__ __forceinline__ int ranges_of(int N) {
+    int r = kMinRanges;
+    while (r < kRanges && N >= 64 * r) r <<= 1;
+    return r;
+}
+
 struct EvalCtx {
     const QueryDev* q;
     int32_t c0, Cl;        // channel slice [c0, c0 + Cl)
@@ -59,7 +67,7 @@ struct EvalCtx {
     int32_t CH, nCh;                   // channels per staged item, items per point
     int32_t L;                         // lanes sharing one point when a whole point is one item (nCh == 1)
     int32_t n0, n1;                    // this CTA's share of the points: [n0, n1)
-    int32_t range_len;                 // points per fixed reduction range (kRanges ranges cover N)
+    int32_t nranges, range_len;        // fixed reduction ranges of this query (ranges_of(N)), points per range
     int32_t csize, crank;              // thread-block cluster working on this query (or: tasks of this evaluation)
     double* part_out;                  // task scheduler: this task's partial sums go here (global), no combine
     bool limit_given;                  // task scheduler: sh.limit already holds the ratio-test limit

@@ -18,8 +18,8 @@ for l in sys.stdin:
   done
   unset FMPNP_LIB
 }
-one --config geman_lm --points 8192 --channels 128 --queries 296
-one --config geman_lm --points 8192 --channels 64 --queries 296
-one --config pyramid --points 8192 --queries 256
+one --config geman_lm --channels 1024 --points 256 --map 64 --queries 2048
+one --config geman_lm --channels 2048 --points 512 --map 64 --queries 1024
+one --config geman_lm --channels 2048 --points 128 --map 64 --queries 1024
 one --queries 256
 cat $out
