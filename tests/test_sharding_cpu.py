@@ -21,6 +21,14 @@ def _free_port():
     return p
 
 
+def test_host_near_gpu_is_a_no_op_without_nvml_or_gpu():
+    from fmpnp_b200.sharding import host_near_gpu
+    before = os.sched_getaffinity(0)
+    with host_near_gpu(0) as h:
+        assert h.cores is None or h.cores <= len(before)
+    assert os.sched_getaffinity(0) == before
+
+
 def test_shard_range_covers_everything():
     from fmpnp_b200.sharding import shard_range
     for B in (0, 1, 5, 16, 17, 256, 16384):
@@ -62,6 +70,11 @@ def _worker(rank, world, port, names, q):
         rec[i]["status"] = o["status"]
     local = torch.from_numpy(rec.view(np.uint8).reshape(hi - lo, RESULT_DTYPE.itemsize).copy())
     allrec = records_to_numpy(gather_result_records(local, B), RESULT_DTYPE)
+    # the asynchronous form (what bench.py uses so that ranks do not run in lock-step) returns the same records
+    again, work = gather_result_records(local, B, async_op=True)
+    if work is not None:
+        work.wait()
+    assert np.array_equal(records_to_numpy(again, RESULT_DTYPE).view(np.uint8), allrec.view(np.uint8))
     if rank == 0:
         q.put((allrec["best_cost"].tolist(), allrec["best_num_inliers"].tolist(), allrec["R"].tolist()))
     dist.barrier()
