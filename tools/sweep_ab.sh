@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B of two builds of the library on the same box.  Usage: tools/sweep_ab.sh <tag> [prev.so]
+# A/B of two builds of the library on the same box.  Usage: tools/sweep_ab.sh <tag> [prev.so] -- bench args are the cases below
 tag=${1:-ab}
 prev=${2:-featuremetric-pnp_b200/lib/libfmpnp_prev.so}
 out=gpurun_out/${tag}.txt
@@ -13,13 +13,11 @@ import sys, json
 for l in sys.stdin:
     l=l.strip()
     if l.startswith('{'):
-        d=json.loads(l); print(d['value'], d['ms_per_step'], d['roofline']['frac'])
+        d=json.loads(l); print(d['value'], d['ms_per_step'], d['roofline']['frac'], d['roofline']['kernel_ms'], d['clocks'])
 " >> $out
   done
   unset FMPNP_LIB
 }
-one --config geman_lm --channels 1024 --points 256 --map 64 --queries 2048
-one --config geman_lm --channels 2048 --points 512 --map 64 --queries 1024
-one --config geman_lm --channels 2048 --points 128 --map 64 --queries 1024
-one --queries 256
+one --config geman_lm --queries 256
+one --config geman_lm --points 8192 --channels 128 --queries 296
 cat $out
