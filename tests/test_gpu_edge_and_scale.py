@@ -419,3 +419,37 @@ def test_full_size_fixed_point_and_determinism(big_scenes):
     assert np.all(c["n_evaluations"] == 1 + 3 * 21)
     costs, nsup = fm().compute_cost_batch(probs)
     assert np.allclose(c["initial_cost"], costs.cpu().numpy(), rtol=0, atol=0)
+
+
+def test_two_contexts_on_two_streams_at_once():
+    """Two host threads, each with its own context and CUDA stream, refine different batches at the same time:
+    the CTAs of the second launch only become resident as those of the first retire, which the scheduler must
+    tolerate (queries are started from a counter by whichever CTA is running).  Records equal the solo runs."""
+    import threading
+    scs = [synth().make_scene(900 + i, N=700, C=256, Hf=16, Wf=16, im_width=128, im_height=128,
+                              K=((50.0, 0.0, 63.5), (0.0, 50.0, 62.3), (0.0, 0.0, 1.0)), grad_scale=1.0 / 64,
+                              outlier_frac=0.1) for i in range(6)]
+    probs = [to_problem(sc) for sc in scs]
+    batches = [[probs[i % 6] for i in range(400)], [probs[(i + 3) % 6] for i in range(333)]]
+    kw = dict(loss="geman_mcclure_loss", lambda_=0.01, ratio_threshold=0.8)
+    solo = [fm().refine_batch(b, 8, **kw)["results"] for b in batches]
+    out, errs = [None, None], []
+
+    def worker(j):
+        try:
+            ctx = fm().Context()
+            with torch.cuda.stream(torch.cuda.Stream()):
+                for _ in range(3):
+                    out[j] = fm().refine_batch(batches[j], 8, ctx=ctx, **kw)["results"]
+            ctx.close()
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+
+    ts = [threading.Thread(target=worker, args=(j,)) for j in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=100)
+    assert not errs, errs
+    for j in range(2):
+        assert out[j] is not None and same_records(out[j], solo[j]), "batch %d differs when run concurrently" % j
