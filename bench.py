@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-adapter-e2e", action="store_true")
     ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
+    ap.add_argument("--gather-every-row", action="store_true",
+                    help="time the refinement with fmpnp_options.gather_every_row = 1 (no record reuse) as the main arm")
     ap.add_argument("--skew-maps", type=int, default=0,
                     help="experiment: place F, Gx, Gy of a query in one buffer, Gx / Gy displaced by this many extra rows "
                          "(0 = three separate allocations, as the product's callers have them)")
@@ -291,14 +293,15 @@ def main():
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
 
-    def step(i=None):
+    def step(i=None, every_row=args.gather_every_row, kev=kev):
         """find_inliers -> active mask (written in place by the kernel), then the refinement kernel."""
         if cfg["inlier_mask"]:
             fm.find_inliers_batch(probs_noact, 0.8, loss=cfg["loss"], ctx=ctx, out=active)
         if i is not None:
             kev[i][0].record()
         fm.refine_batch(probs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
-                        ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=res_dev)
+                        ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=res_dev,
+                        gather_every_row=every_row)
         if i is not None:
             kev[i][1].record()
         if world > 1:  # the single exchange of the path: result records, on NCCL's own stream (no lock-step)
@@ -344,7 +347,9 @@ def main():
 
     # ---- roofline of the dominant kernel (refine_tasks_kernel), from the last step's results
     res = res_dev.cpu().numpy().view(RESULT_DTYPE).reshape(B)
-    alg_bytes = float(res["gathered_rows"].astype(np.float64).sum()) * 4.0
+    gath_bytes = float(res["gathered_rows"].astype(np.float64).sum()) * 4.0    # rows the launch actually read
+    reused_bytes = float(res["reused_rows"].astype(np.float64).sum()) * 4.0    # rows it did not have to read again
+    alg_bytes = gath_bytes + reused_bytes  # every supported point's 4 rows at every evaluation
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
@@ -365,11 +370,61 @@ def main():
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernel_ms": k_ms,
                 "algorithmic_bytes_per_launch": alg_bytes,
+                "gathered": {"bytes_per_launch": gath_bytes, "gbs": gath_bytes / (k_ms / 1e3) / 1e9,
+                             "frac_of_peak": gath_bytes / (k_ms / 1e3) / 1e9 / peak,
+                             "reused_fraction_of_rows": reused_bytes / max(alg_bytes, 1.0),
+                             "note": "the reference's lookup is nearest-cell (model.py:74-97): a point that projects "
+                                     "into the same cell as at its previous evaluation keeps its record (bit-identical) "
+                                     "and its rows are not read again; `achieved` counts the contract's algorithmic "
+                                     "bytes (4 rows per supported point per evaluation), `gathered` the bytes read"},
                 "nominal_bytes_per_launch": float(nominal) if levels is None else None,
                 "share_of_step": k_ms * args.steps / total_ms, "geometry": geo,
                 "kernel_ms_all": [round(x, 3) for x in kern_ms],
                 "peak_note": "peak is the measured COPY bandwidth (half reads, half writes); this kernel only reads, "
-                             "so frac can exceed 1 - see dram__cycles_active in profiles/ for the remaining headroom"}
+                             "so frac can exceed 1 - see dram__cycles_active in profiles/ for the remaining headroom; "
+                             "with record reuse (default) frac counts algorithmic bytes that were never read - the "
+                             "memory-system figure is `gathered`, the HBM-bound regime is `every_row_gathered`"}
+    if args.gather_every_row:
+        traffic_key = "refine_kernel_dram_bytes_per_launch_every_row"
+    else:
+        traffic_key = "refine_kernel_dram_bytes_per_launch"
+    if os.path.exists(tpath):
+        try:
+            roofline["traffic"] = json.load(open(tpath)).get(traffic_key)
+        except Exception:
+            roofline["traffic"] = None
+
+    # ---- the same launch with every row gathered at every evaluation (no record reuse): the HBM-bound regime
+    if not args.gather_every_row:
+        kev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for _ in range(2):
+            step(every_row=True)
+        drain()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s2.record()
+        for i in range(args.steps):
+            step(i, every_row=True, kev=kev2)
+        drain()
+        e2.record()
+        torch.cuda.synchronize()
+        t2 = s2.elapsed_time(e2)
+        if world > 1:
+            tm2 = torch.tensor([t2], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm2, op=dist.ReduceOp.MAX)
+            t2 = float(tm2.item())
+        res2 = res_dev.cpu().numpy().view(RESULT_DTYPE).reshape(B)
+        k2 = float(np.mean([a.elapsed_time(b) for a, b in kev2]))
+        b2 = float(res2["gathered_rows"].astype(np.float64).sum()) * 4.0
+        same = all(np.ascontiguousarray(res[f]).tobytes() == np.ascontiguousarray(res2[f]).tobytes()
+                   for f in res.dtype.names if f not in ("gathered_rows", "reused_rows"))
+        roofline["every_row_gathered"] = {
+            "value": world * B * args.steps / (t2 / 1e3), "unit": UNIT, "ms_per_step": t2 / args.steps, "kernel_ms": k2,
+            "bytes_per_launch": b2, "achieved": b2 / (k2 / 1e3) / 1e9, "frac": b2 / (k2 / 1e3) / 1e9 / peak,
+            "results_bit_identical_to_default": bool(same),
+            "note": "fmpnp_options.gather_every_row = 1: 4*N*C*4 bytes read per iteration, same results"}
 
     # context for the fraction: what plain library kernels stream on THIS GPU right now (not the contract's peak)
     try:

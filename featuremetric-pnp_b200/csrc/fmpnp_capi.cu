@@ -50,6 +50,9 @@ struct fmpnp_ctx {
     int smem_configured = -1;
     Geometry_last last = {0, 0, 0, 0};
     int64_t launches = 0;
+    // record reuse: generations handed out so far (tags of `d_rec` hold generation << 32 | cell, never generation 0)
+    uint64_t reuse_next = 1;
+    int reuse = 1;  // FMPNP_REUSE=0: gather every row at every evaluation, whatever the options say
 };
 
 namespace {
@@ -153,6 +156,8 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
         ctx->cap_points = 0;
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_rec, need * kRecDoubles * sizeof(double)));
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_supp, need));
+        // no record tag of the new buffer may look like a generation that is handed out later
+        FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_rec, 0, need * kRecDoubles * sizeof(double), stream));
         ctx->cap_points = need;
     }
     *n_max_out = n_max;
@@ -348,6 +353,7 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     ctx->watchdog_s = env_int("FMPNP_WATCHDOG_S", 20);
     if (ctx->watchdog_s < 0) ctx->watchdog_s = 0;
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
+    ctx->reuse = env_int("FMPNP_REUSE", 1);
     *out = ctx;
     return FMPNP_SUCCESS;
 }
@@ -436,6 +442,17 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     memcpy(lp.levels, o->levels, sizeof(lp.levels));
     lp.solver = o->solver;
     lp.results = results;
+    lp.reuse = (ctx->reuse != 0 && o->gather_every_row == 0) ? 1 : 0;
+    {  // one generation per (query, level) of this launch; generations are never handed out twice
+        const uint64_t gens = (uint64_t)B * (uint64_t)levels_eff;
+        if (ctx->reuse_next + gens >= (1ull << 32)) {
+            FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_rec, 0, ctx->cap_points * kRecDoubles * sizeof(double), stream));
+            ctx->reuse_next = 1;
+        }
+        if (gens >= (1ull << 32) - 1) lp.reuse = 0;
+        lp.reuse_base = (uint32_t)ctx->reuse_next;
+        ctx->reuse_next += gens;
+    }
     if (hist) {
         lp.hist.enabled = 1;
         lp.hist.cap = hist->cap;

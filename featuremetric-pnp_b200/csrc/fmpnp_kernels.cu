@@ -88,6 +88,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.crank = crank;
         c.part_out = nullptr;
         c.limit_given = false;
+        c.reuse_gen = 0u;
         {
             c.nranges = ranges_of(q.N);
             const int per = max(1, (q.N + c.nranges - 1) / c.nranges);
@@ -105,6 +106,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
             for (int i = 0; i < 3; ++i) sh.t[i] = q.t0[i];
             sh.n_evals = 0;
             sh.gathered = 0;
+            sh.reused = 0;
         }
         __syncthreads();
 
@@ -180,6 +182,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
             c.alpha = p.alpha;
             c.ratio_mode = p.use_ratio ? 1 : 0;
             c.thr = p.ratio_thr;
+            c.reuse_gen = p.reuse ? p.reuse_base + (uint32_t)(qi * nlev + lvl) : 0u;  // records of this level only
 
             // ---- i == 0: cost and linearisation at the incoming pose (model.py:303-359)
             hist_slices(p, qi, sh.hist_len, c);
@@ -323,6 +326,7 @@ __device__ __forceinline__ void load_state(Shared& sh, const volatile QueryState
     sh.lr = g.lr;
     sh.initial_cost = g.initial_cost;
     sh.gathered = g.gathered;
+    sh.reused = g.reused;
     sh.best_n = g.best_n;
     sh.has_best = g.has_best;
     sh.status = g.status;
@@ -351,6 +355,7 @@ __device__ __forceinline__ void store_state(const Shared& sh, QueryState& g) {
     g.lr = sh.lr;
     g.initial_cost = sh.initial_cost;
     g.gathered = sh.gathered;
+    g.reused = sh.reused;
     g.best_n = sh.best_n;
     g.has_best = sh.has_best;
     g.status = sh.status;
@@ -413,7 +418,8 @@ __device__ __forceinline__ void combine_parts(Shared& sh, const double* part, in
     } else if (tid >= 32 && tid < 34) {
         long long sum = 0;
         for (int r = 0; r < units; ++r) sum += __ldcg(reinterpret_cast<const long long*>(part + (size_t)r * kPartStride) + 28 + (tid - 32));
-        (&sh.ev_count)[tid - 32] = (int32_t)sum;
+        (&sh.ev_count)[tid - 32] = (int32_t)(sum & 0xffffffffll);          // survivors / supported
+        if (tid == 33) sh.ev_ngath = (int32_t)(sum >> 32);                 // gathered rides in the high half of slot 29
     }
     __syncthreads();
     if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;
@@ -447,6 +453,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         g.lr = 1.0;
         g.initial_cost = NAN;
         g.gathered = 0;
+        g.reused = 0;
         g.best_n = -1;
         g.has_best = 0;
         g.status = FMPNP_STATUS_OK;
@@ -508,6 +515,9 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.thr = p.ratio_thr;
         const bool grad = gv.ev_grad != 0;
         const int hist_entry = gv.ev_hist;
+        c.reuse_gen = (MODE == kModeRefine && p.reuse && grad)
+                          ? p.reuse_base + (uint32_t)(qi * (p.n_levels > 0 ? p.n_levels : 1) + gv.level)
+                          : 0u;
         c.aligned = slice_aligned(q, c.c0, c.Cl, grad);
         c.inl_out = MODE == kModeFindInliers ? p.inliers_out + (size_t)qi * p.inliers_stride : nullptr;
         c.h_px = nullptr;
@@ -606,7 +616,8 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             reduce_points<false>(c, evpose, evpose + 9, sh, rp);
         if (tid == 0) {
             sh.n_evals += 1;
-            sh.gathered += (long long)sh.ev_nsup * c.Cl * (grad ? 4 : 2);
+            sh.gathered += (long long)sh.ev_ngath * c.Cl * (grad ? 4 : 2);
+            sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (grad ? 4 : 2);
         }
         __syncthreads();
 

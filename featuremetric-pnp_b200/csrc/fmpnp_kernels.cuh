@@ -10,7 +10,8 @@ namespace fmpnp {
 
 constexpr int kWarps = 8;                         // each streams its own points through its slice of the ring
 constexpr int kThreads = kWarps * 32;             // 256
-constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by (+2 pad) = 64 B
+constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by, reuse tag (+1 pad) = 64 B
+constexpr int kRecTagSlot = 6;                    // the record's tag: (generation << 32 | cell) it was gathered for
 constexpr int kRanges = 128;                      // max fixed reduction ranges per query == max tasks per evaluation
 constexpr int kMinRanges = 16;                    // min (small queries) == max cluster size
 constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
@@ -58,7 +59,7 @@ struct __align__(16) QueryState {
     double prev_cost, best_cost, lambda, lr, initial_cost;
     double evR[9], evt[3];  // pose of the evaluation in flight
     double ev_limit;        // its ratio-test limit (published between round 0 and round 1)
-    long long gathered;
+    long long gathered, reused;
     int32_t best_n, has_best, status, flag, hist_len, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
     int32_t phase, level, it;
@@ -107,6 +108,13 @@ struct LaunchParams {
     int32_t cluster_size;   // CTAs per query (thread-block cluster); grid = clusters * cluster_size
     SchedDev sched;         // task scheduler (scheduler == 1): rec / supp are then per QUERY, not per CTA
     int32_t scheduler;      // 0: one CTA (or cluster) per query, 1: task queue
+    // Record reuse.  The reference looks features up at the NEAREST cell (indexing_, model.py:74-97), so a point's
+    // record (its six channel sums) is a function of (point, cell, channel slice) only: while a point stays in
+    // its cell from one evaluation to the next the record in `rec` is still the right one, bit for bit, and its
+    // rows are not gathered again.  A record carries the tag (generation << 32 | cell); the generation is unique
+    // per (launch, query, level) -- reuse_base + query * levels + level -- so nothing stale can ever match.
+    int32_t reuse;          // 0: gather every row at every evaluation
+    uint32_t reuse_base;    // first generation of this launch (never 0)
 };
 
 // Host-side launchers (defined in fmpnp_kernels.cu)

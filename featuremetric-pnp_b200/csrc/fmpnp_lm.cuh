@@ -14,7 +14,8 @@ __device__ __forceinline__ void evaluate(EvalCtx& c, const double* R, const doub
     reduce_points<GRAD>(c, R, t, sh, rp);
     if (threadIdx.x == 0) {
         sh.n_evals += 1;
-        sh.gathered += (long long)sh.ev_nsup * c.Cl * (GRAD ? 4 : 2);
+        sh.gathered += (long long)sh.ev_ngath * c.Cl * (GRAD ? 4 : 2);
+        sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (GRAD ? 4 : 2);
     }
 }
 
@@ -163,6 +164,7 @@ __device__ __forceinline__ void write_result(const Shared& sh, const LaunchParam
     r.n_evaluations = sh.n_evals;
     for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) r.level_status[i] = sh.level_status[i];
     r.gathered_rows = sh.gathered;
+    r.reused_rows = sh.reused;
     if (p.hist.enabled) p.hist.len[qi] = sh.hist_len;
 }
 

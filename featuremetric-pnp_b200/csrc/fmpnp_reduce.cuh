@@ -132,7 +132,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     const int wact = nr >= kWarps ? kWarps : nr;     // ... of the warps that own any
     double* const wscr = reinterpret_cast<double*>(c.ring + (size_t)warp * c.ring_per_warp);  // idle ring slice
     double* const stack = wscr + 28 * kLaneStride;
-    int32_t cnt[2] = {0, 0};  // survivors, supported (this lane, all its ranges)
+    int32_t cnt[3] = {0, 0, 0};  // survivors, supported, supported and gathered by this evaluation (this lane, all its ranges)
     if (warp < wact) {
         for (int rr = 0; rr < rpw; ++rr) {
             const int r0 = min(q.N, (r_first + warp * rpw + rr) * per), r1 = min(q.N, r0 + per);
@@ -140,10 +140,12 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
 #pragma unroll
             for (int i = 0; i < 28; ++i) acc[i] = 0.0;
             for (int n = r0 + lane; n < r1; n += 32) {
-                const bool sup = __ldcg(c.supp + n) != 0;
+                const uint8_t sflag = __ldcg(c.supp + n);
+                const bool sup = sflag != 0;
                 bool keep = false;
                 if (sup) {
                     ++cnt[1];
+                    cnt[2] += sflag == 1;
                     const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
                     const double2 rc0 = __ldcg(r);
                     const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
@@ -191,16 +193,17 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         }
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 3; ++i) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) cnt[i] += __shfl_xor_sync(0xffffffffu, cnt[i], off);
     }
     if (lane == 0) {
         sh.red_i[warp][0] = cnt[0];
         sh.red_i[warp][1] = cnt[1];
+        sh.red_i[warp][2] = cnt[2];
     }
     __syncthreads();
-    int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup are adjacent
+    int32_t* iout = &sh.ev_count;  // ev_count, ev_nsup, ev_ngath are adjacent
     if (tid < 28) {  // pairwise tree over the warps that own ranges
         double v[kWarps];
 #pragma unroll
@@ -218,12 +221,18 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
             sh.cpart[rp.cpar][tid] = v[0];
         else
             sh.ev[tid] = v[0];
-    } else if (tid >= 32 && tid < 34) {
+    } else if (tid >= 32 && tid < 35) {
         int32_t tot_i = 0;
         for (int w = 0; w < kWarps; ++w) tot_i += sh.red_i[w][tid - 32];
-        if (c.part_out)
-            reinterpret_cast<long long*>(c.part_out)[28 + (tid - 32)] = tot_i;
-        else if (c.csize > 1)
+        if (c.part_out) {  // two int64 slots: survivors; supported (low half) + gathered (high half), see combine_parts
+            if (tid == 33) {
+                int32_t ng = 0;
+                for (int w = 0; w < kWarps; ++w) ng += sh.red_i[w][2];
+                reinterpret_cast<long long*>(c.part_out)[29] = (long long)tot_i + ((long long)ng << 32);
+            } else if (tid == 32) {
+                reinterpret_cast<long long*>(c.part_out)[28] = tot_i;
+            }
+        } else if (c.csize > 1)
             sh.cpart_i[rp.cpar][tid - 32] = tot_i;
         else
             iout[tid - 32] = tot_i;
@@ -233,7 +242,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
         return;
     }
     if (c.csize > 1)
-        cluster_combine<false>(sh, c.csize, rp.cpar, 28, sh.ev, 2, iout);
+        cluster_combine<false>(sh, c.csize, rp.cpar, 28, sh.ev, 3, iout);
     else
         __syncthreads();
     if (tid == 0) sh.ev_cost = sh.ev[27] / (double)sh.ev_count;  // mean; 0/0 = NaN like torch's empty mean

@@ -21,11 +21,12 @@ struct __align__(16) Shared {
     double climit;
     double cpart[2][32];  // this CTA's partial sums, read by the other CTAs of the cluster (double-buffered)
     double prev_cost, best_cost, lambda, lr, ev_cost, limit, initial_cost;
-    long long gathered;
+    long long gathered, reused;
     int32_t red_i[kWarps][4];
     int32_t cpart_i[2][4];
     int32_t climit_nan;
-    int32_t ev_count, ev_nsup, best_n, has_best, status, flag, hist_len, query, n_evals, initial_set;
+    int32_t ev_count, ev_nsup, ev_ngath;  // survivors, supported, supported and gathered (not reused); adjacent
+    int32_t best_n, has_best, status, flag, hist_len, query, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
     // --- the supported points of the two batches a warp works on (double-buffered): cell and index
     int32_t bl_cell[kWarps][2][32];
@@ -56,7 +57,8 @@ struct EvalCtx {
     int32_t ratio_mode;    // 0 none, 1 on rho (forward / find_inliers), 2 on raw SSD (compute_cost)
     double thr;
     double* rec;           // per-point records of this CTA
-    uint8_t* supp;         // per-point support flags of this CTA
+    uint8_t* supp;         // per-point support flags of this CTA: 0 unsupported, 1 gathered, 2 record reused
+    uint32_t reuse_gen;    // generation of the record tags this evaluation may reuse (0 = gather every row)
     int32_t* h_px;         // history slices for the entry being evaluated (or null)
     uint8_t* h_mask;
     uint8_t* h_kept;
@@ -128,13 +130,27 @@ __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const doub
     const double x = q.pts[3 * n + 0], y = q.pts[3 * n + 1], z = q.pts[3 * n + 2];
     const Proj pr = project_point(R, t, q.K, x, y, z, q.im_w, q.im_h);
     const bool sup = act && pr.supported;
-    c.supp[n] = sup ? 1 : 0;
     if (c.h_px) {
         c.h_px[2 * n + 0] = pr.px;
         c.h_px[2 * n + 1] = pr.py;
         c.h_mask[n] = sup ? 1 : 0;
     }
-    return sup ? cell_index(pr.px, pr.py, q.Hf, q.Wf, q.im_w, q.im_h) : -1;
+    int32_t cell = sup ? cell_index(pr.px, pr.py, q.Hf, q.Wf, q.im_w, q.im_h) : -1;
+    uint8_t flag = sup ? 1 : 0;
+    if (c.reuse_gen != 0u && sup) {
+        // nearest-cell lookup (model.py:74-97): same cell, same slice => same rows => the record the point already
+        // has is the one this evaluation would compute.  .cg: another CTA may have written it (task scheduler).
+        long long* tag = reinterpret_cast<long long*>(c.rec + (size_t)n * kRecDoubles + kRecTagSlot);
+        const long long want = (long long)(((unsigned long long)c.reuse_gen << 32) | (unsigned int)cell);
+        if (__ldcg(tag) == want) {
+            flag = 2;
+            cell = -1;  // nothing to gather
+        } else {
+            __stcg(tag, want);  // its rows are gathered by this evaluation (the record follows before anyone reads it)
+        }
+    }
+    c.supp[n] = flag;
+    return cell;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -33,14 +33,14 @@ class COptions(C.Structure):
     _fields_ = [("n_iters", C.c_int32), ("loss_id", C.c_int32), ("barron_alpha", C.c_double),
                 ("lambda0", C.c_double), ("ratio_threshold", C.c_double), ("n_levels", C.c_int32),
                 ("levels", (C.c_int32 * 2) * MAX_LEVELS), ("solver", C.c_int32), ("cluster_size", C.c_int32),
-                ("reserved", C.c_int32 * 6)]
+                ("gather_every_row", C.c_int32), ("reserved", C.c_int32 * 5)]
 
 
 class CResult(C.Structure):
     _fields_ = [("R", C.c_double * 9), ("t", C.c_double * 3), ("best_cost", C.c_double),
                 ("initial_cost", C.c_double), ("best_num_inliers", C.c_int32), ("status", C.c_int32),
                 ("n_evaluations", C.c_int32), ("level_status", C.c_int32 * MAX_LEVELS),
-                ("gathered_rows", C.c_int64)]
+                ("gathered_rows", C.c_int64), ("reused_rows", C.c_int64)]
 
 
 class CHistory(C.Structure):
@@ -243,9 +243,11 @@ def _problem_array(problems):
     return arr
 
 
-def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None, cluster_size=0):
+def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None, cluster_size=0,
+             gather_every_row=False):
     o = COptions()
     o.cluster_size = int(cluster_size)
+    o.gather_every_row = 1 if gather_every_row else 0
     lid, alpha = loss_id_of(loss)
     if barron_alpha is not None:
         alpha = float(barron_alpha)
@@ -267,8 +269,12 @@ def _stream_ptr():
 
 
 def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_threshold=None, levels=None,
-                 track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None, cluster_size=0):
+                 track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None, cluster_size=0,
+                 gather_every_row=False):
     """Batched sparseFeaturePnP.forward (levels=None) / multilevel_optimization (levels=[(s, e), ...]).
+
+    gather_every_row=True reads the rows of every supported point at every evaluation; the default keeps the
+    record of a point that stays in its feature-map cell (bit-identical results, see include/fmpnp.h).
 
     Returns a dict: `results` (numpy structured array, one fmpnp_result per query, on the host if
     sync else None), `results_dev` (raw device tensor), and with track=True `history` (dict of
@@ -276,7 +282,7 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     ctx = ctx or default_context()
     B = len(problems)
     dev = torch.device("cuda", ctx.device)
-    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size)
+    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size, gather_every_row)
     arr = _problem_array(problems)
     res_dev = out if out is not None else torch.empty((max(B, 1), RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
     hist, hbuf = None, None

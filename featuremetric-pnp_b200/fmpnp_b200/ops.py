@@ -16,7 +16,7 @@ kernel behind them.
       track     : bool; True also returns the per-iteration history (the reference's track_)
       active    : [] or one (N,) uint8 CUDA mask per query: points with 0 are left out (== pts3D[inliers])
       returns   : [results] or [results, len, Rs, ts, costs, points2d, mask, kept]; results is a
-                  (B, 168) uint8 CUDA tensor of fmpnp_result records (view with binding.RESULT_DTYPE)
+                  (B, 176) uint8 CUDA tensor of fmpnp_result records (view with binding.RESULT_DTYPE)
 """
 from typing import List
 

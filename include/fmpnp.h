@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define FMPNP_VERSION 100
+#define FMPNP_VERSION 101
 #define FMPNP_MAX_LEVELS 8
 
 typedef struct fmpnp_ctx fmpnp_ctx;
@@ -109,7 +109,12 @@ typedef struct {
     int32_t cluster_size;   /* 0 = automatic: the task scheduler (an evaluation is cut into tasks that any CTA
                                can run; every CTA stays busy for any batch size).  1, 2, 4, 8 or 16 = refine
                                each query with one thread-block cluster of that many CTAs instead */
-    int32_t reserved[6];
+    int32_t gather_every_row; /* 0 (default): a point that projects into the same cell as at its previous evaluation
+                               keeps its record -- the reference's lookup is nearest-cell (indexing_,
+                               model.py:74-97), so the record is a function of (point, cell, channel slice) and
+                               the result is bit-identical; its rows are not read again.  1: gather the rows of
+                               every supported point at every evaluation (4 N C 4 bytes per iteration) */
+    int32_t reserved[5];
 } fmpnp_options;
 
 /* What the callers read back (sparse_to_dense_predictor.py:257): the returned pose,
@@ -124,8 +129,10 @@ typedef struct {
     int32_t status;            /* FMPNP_STATUS_* of the last level */
     int32_t n_evaluations;     /* pose evaluations performed (1 + trial steps per level, + 1 for compute_cost) */
     int32_t level_status[FMPNP_MAX_LEVELS];
-    int64_t gathered_rows;     /* sum over evaluations of (supported points x channels x maps read):
-                                  x 4 B = algorithmic bytes of this query (bench roofline) */
+    int64_t gathered_rows;     /* sum over evaluations of (points whose rows were read x channels x maps read):
+                                  x 4 B = bytes this query gathered (bench roofline) */
+    int64_t reused_rows;       /* the same count for the supported points whose record was reused instead;
+                                  gathered_rows + reused_rows = sum of (supported points x channels x maps) */
 } fmpnp_result;
 
 /* Optional per-iteration history == the reference's `track_` dict (model.py:170-176):

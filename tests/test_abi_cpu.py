@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
     L = ctypes.CDLL(fm.lib_path())
     for n in names:
         assert hasattr(L, n), "libfmpnp.so does not export " + n
-    assert fm.lib().fmpnp_version() == 100
+    assert fm.lib().fmpnp_version() == 101
 
 
 def test_struct_sizes_match_the_c_abi():
@@ -100,4 +100,4 @@ def test_header_is_plain_c_and_links_against_the_library(tmp_path):
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
                     str(src), "-o", str(exe), "-L", libdir, "-lfmpnp", "-Wl,-rpath," + libdir], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
-    assert int(out[0]) == 100 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)
+    assert int(out[0]) == 101 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)

@@ -20,11 +20,27 @@ def fm():
     return fmpnp_b200
 
 
-def same_records(a, b):
+def same_records(a, b, skip=()):
     """Field-wise bit equality of fmpnp_result records (the struct has 4 padding bytes)."""
     a, b = np.atleast_1d(a), np.atleast_1d(b)
     return a.shape == b.shape and all(
-        np.ascontiguousarray(a[f]).tobytes() == np.ascontiguousarray(b[f]).tobytes() for f in a.dtype.names)
+        np.ascontiguousarray(a[f]).tobytes() == np.ascontiguousarray(b[f]).tobytes() for f in a.dtype.names
+        if f not in skip)
+
+
+def assert_reuse_is_invisible(out, full, B):
+    """`out` (records of points that stay in their cell are reused) against `full` (gather_every_row=True): the
+    same bits in every result field and history entry; only the row counters tell the two apart."""
+    assert same_records(out["results"], full["results"], skip=("gathered_rows", "reused_rows"))
+    g, r = out["results"]["gathered_rows"], out["results"]["reused_rows"]
+    assert np.array_equal(g + r, full["results"]["gathered_rows"]) and not full["results"]["reused_rows"].any()
+    assert (g >= 0).all() and (r >= 0).all()
+    if "history" in out:
+        for b in range(B):
+            n = int(out["history"]["len"][b])
+            assert n == int(full["history"]["len"][b])
+            for k in ("Rs", "ts", "costs", "points2d", "mask", "kept"):
+                assert np.array_equal(out["history"][k][b, :n], full["history"][k][b, :n], equal_nan=k in ("Rs", "ts", "costs")), k
 
 
 def synth():
@@ -392,7 +408,12 @@ def test_full_size_first_step_against_torch_fp64(big_scenes):
         cost1, _, _, px1, m1 = torch_eval(sc, Rn, tn)
         assert np.array_equal(h["points2d"][0, 1], px1) and np.array_equal(h["mask"][0, 1].astype(bool), m1)
         assert abs(h["costs"][0, 1] - cost1) <= 1e-11 * abs(cost1)
-        assert int(r["gathered_rows"]) == (int(m.sum()) + int(m1.sum())) * 1024 * 4
+        assert int(r["gathered_rows"]) + int(r["reused_rows"]) == (int(m.sum()) + int(m1.sum())) * 1024 * 4
+        cell = lambda px_: (px_[:, 1] * 128 // 1024) * 128 + px_[:, 0] * 128 // 1024
+        stay = m & m1 & (cell(px) == cell(px1))  # supported twice, same cell: the record is kept
+        assert int(r["reused_rows"]) == int(stay.sum()) * 1024 * 4
+        full = fm().refine_batch([p], 1, loss="squared_loss", lambda_=0.01, track=True, gather_every_row=True)
+        assert_reuse_is_invisible(out, full, 1)
 
 
 def test_full_size_fixed_point_and_determinism(big_scenes):

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from test_gpu_edge_and_scale import compare, fm, run_oracle, same_records, synth, to_problem
+from test_gpu_edge_and_scale import assert_reuse_is_invisible, compare, fm, run_oracle, same_records, synth, to_problem
 
 pytestmark = pytest.mark.gpu
 LOSSES = ["squared_loss", "huber_loss", "cauchy_loss", "geman_mcclure_loss"]
@@ -45,6 +45,7 @@ def test_random_ragged_batches(seed):
         o = run_oracle(sc, cfg["n_iters"], cfg["loss"], cfg["lambda_"], cfg["ratio"], cfg["levels"])
         compare("seed %d query %d %r" % (seed, i, cfg), out["results"][i], out["history"], o, b=i,
                 use_ratio=cfg["ratio"] is not None)
+    assert_reuse_is_invisible(out, fm().refine_batch(probs, cfg["n_iters"], gather_every_row=True, **kw), len(probs))
     one = fm().refine_batch(probs[:1], cfg["n_iters"], cluster_size=8, **kw)
     assert fm().default_context().last_geometry["tasks_per_evaluation"] == 0
     assert same_records(one["results"][0], out["results"][0]), "cluster route differs from scheduler route: %r" % (cfg,)
