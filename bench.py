@@ -39,7 +39,7 @@ UNIT = "queries/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     # workload overrides (exploration only; the defaults are the contract)
@@ -53,7 +53,11 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-adapter-e2e", action="store_true")
+    ap.add_argument("--no-zero-copy", action="store_true", help="skip the zero-copy e2e variants")
     ap.add_argument("--cpu-queries", type=int, default=0, help="cpu_baseline sample size (0 = auto)")
+    ap.add_argument("--two-calls", action="store_true",
+                    help="cfg2: fmpnp_find_inliers_batch + fmpnp_refine_batch(active = mask) instead of one launch with "
+                         "fmpnp_options.inlier_threshold")
     ap.add_argument("--gather-every-row", action="store_true",
                     help="time the refinement with fmpnp_options.gather_every_row = 1 (no record reuse) as the main arm")
     ap.add_argument("--skew-maps", type=int, default=0,
@@ -123,7 +127,7 @@ class ClockSampler:
                         self.reasons.add(n)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.004)  # a step takes a few milliseconds
 
     def __enter__(self):
         if self.nv is not None:
@@ -284,24 +288,28 @@ def main():
             sc.pts3D = sc.pts3D[order].contiguous()
             sc.ref = sc.ref[order].contiguous()
     active = torch.ones((B, args.points), dtype=torch.uint8, device=dev) if cfg["inlier_mask"] else None
-    probs = [fm.Problem.from_scene(sc, active=active[i] if active is not None else None) for i, sc in enumerate(scenes)]
-    probs_noact = [fm.Problem.from_scene(sc) for sc in scenes]
+    # descriptors marshalled once (fmpnp_problem array in host memory); every call still stages them to the device
+    probs = fm.ProblemBatch([fm.Problem.from_scene(sc, active=active[i] if active is not None else None)
+                             for i, sc in enumerate(scenes)])
+    probs_noact = fm.ProblemBatch([fm.Problem.from_scene(sc) for sc in scenes])
     torch.cuda.synchronize()
     gen_s = time.perf_counter() - t_gen
     res_dev = torch.empty((B, RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
 
+    fused = bool(cfg["inlier_mask"]) and not args.two_calls
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
 
     def step(i=None, every_row=args.gather_every_row, kev=kev):
-        """find_inliers -> active mask (written in place by the kernel), then the refinement kernel."""
-        if cfg["inlier_mask"]:
+        """find_inliers -> refinement of the points it keeps: one launch (inlier_threshold), or with --two-calls the
+        find_inliers kernel (active mask written in place) followed by the refinement kernel."""
+        if cfg["inlier_mask"] and not fused:
             fm.find_inliers_batch(probs_noact, 0.8, loss=cfg["loss"], ctx=ctx, out=active)
         if i is not None:
             kev[i][0].record()
-        fm.refine_batch(probs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+        fm.refine_batch(probs_noact if fused else probs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
                         ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=res_dev,
-                        gather_every_row=every_row)
+                        gather_every_row=every_row, inlier_threshold=0.8 if fused else None)
         if i is not None:
             kev[i][1].record()
         if world > 1:  # the single exchange of the path: result records, on NCCL's own stream (no lock-step)
@@ -350,6 +358,12 @@ def main():
     gath_bytes = float(res["gathered_rows"].astype(np.float64).sum()) * 4.0    # rows the launch actually read
     reused_bytes = float(res["reused_rows"].astype(np.float64).sum()) * 4.0    # rows it did not have to read again
     alg_bytes = gath_bytes + reused_bytes  # every supported point's 4 rows at every evaluation
+    pass_bytes = 0.0
+    if fused:  # the inlier pass is not one of the contract's n_iters + 1 evaluations: leave its rows out of `achieved`
+        _, nsup_all = fm.compute_cost_batch(probs_noact, ctx=ctx)
+        rows = 4 if (levels is None and not args.gather_every_row) else 2
+        pass_bytes = float(nsup_all.double().sum().item()) * args.channels * rows * 4.0
+        alg_bytes -= pass_bytes
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
@@ -369,7 +383,7 @@ def main():
     kname = "fmpnp::refine_tasks_kernel" if geo["tasks_per_evaluation"] else "fmpnp::refine_kernel"
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernel_ms": k_ms,
-                "algorithmic_bytes_per_launch": alg_bytes,
+                "algorithmic_bytes_per_launch": alg_bytes, "inlier_pass_bytes_per_launch": pass_bytes,
                 "gathered": {"bytes_per_launch": gath_bytes, "gbs": gath_bytes / (k_ms / 1e3) / 1e9,
                              "frac_of_peak": gath_bytes / (k_ms / 1e3) / 1e9 / peak,
                              "reused_fraction_of_rows": reused_bytes / max(alg_bytes, 1.0),
@@ -418,6 +432,8 @@ def main():
         res2 = res_dev.cpu().numpy().view(RESULT_DTYPE).reshape(B)
         k2 = float(np.mean([a.elapsed_time(b) for a, b in kev2]))
         b2 = float(res2["gathered_rows"].astype(np.float64).sum()) * 4.0
+        if fused:  # minus the inlier pass (F and ref rows of every supported point), as above
+            b2 -= float(nsup_all.double().sum().item()) * args.channels * 2 * 4.0
         same = all(np.ascontiguousarray(res[f]).tobytes() == np.ascontiguousarray(res2[f]).tobytes()
                    for f in res.dtype.names if f not in ("gathered_rows", "reused_rows"))
         roofline["every_row_gathered"] = {
@@ -454,7 +470,8 @@ def main():
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": dict(cfg, sort_points=bool(args.sort_points), outlier_frac=outl), "roofline": roofline, "clocks": clk.summary(),
+            "dtype": "f64", "data": "synthetic", "config": dict(cfg, sort_points=bool(args.sort_points), outlier_frac=outl,
+                                                               launches_per_step=1 + int(bool(cfg["inlier_mask"]) and not fused)), "roofline": roofline, "clocks": clk.summary(),
             "gpu_launches": int(launches), "input_generation_s": gen_s,
             "status_histogram": {str(k): int(v) for k, v in zip(*np.unique(res["status"], return_counts=True))},
             "mean_evaluations_per_query": float(res["n_evaluations"].mean())}
@@ -468,11 +485,14 @@ def main():
         host = [{k: getattr(scenes[i], k).cpu().pin_memory() for k in names} for i in range(E)]
         devbuf = [{k: torch.empty_like(getattr(scenes[i], k)) for k in names} for i in range(E)]
         act_e = torch.ones((E, args.points), dtype=torch.uint8, device=dev) if cfg["inlier_mask"] else None
-        eprobs = [fm.Problem(devbuf[i]["F"], devbuf[i]["Gx"], devbuf[i]["Gy"], devbuf[i]["ref"], devbuf[i]["pts3D"],
-                             scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024,
-                             active=act_e[i] if act_e is not None else None) for i in range(E)]
-        eprobs_na = [fm.Problem(devbuf[i]["F"], None, None, devbuf[i]["ref"], devbuf[i]["pts3D"], scenes[i].K,
-                                scenes[i].R0, scenes[i].t0, 1024, 1024) for i in range(E)]
+        eprobs = fm.ProblemBatch([fm.Problem(devbuf[i]["F"], devbuf[i]["Gx"], devbuf[i]["Gy"], devbuf[i]["ref"],
+                                             devbuf[i]["pts3D"], scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024,
+                                             active=act_e[i] if act_e is not None else None) for i in range(E)])
+        eprobs_na = fm.ProblemBatch([fm.Problem(devbuf[i]["F"], None, None, devbuf[i]["ref"], devbuf[i]["pts3D"],
+                                                scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024) for i in range(E)])
+        eprobs_gn = fm.ProblemBatch([fm.Problem(devbuf[i]["F"], devbuf[i]["Gx"], devbuf[i]["Gy"], devbuf[i]["ref"],
+                                                devbuf[i]["pts3D"], scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024)
+                                     for i in range(E)])
         eres = torch.empty((E, RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
         eres_host = torch.empty((E, RESULT_DTYPE.itemsize), dtype=torch.uint8).pin_memory()
         h2d = sum(t.numel() * t.element_size() for d in host for t in d.values())
@@ -482,10 +502,11 @@ def main():
             for i in range(E):
                 for k in names:
                     devbuf[i][k].copy_(host[i][k], non_blocking=True)
-            if cfg["inlier_mask"]:
+            if cfg["inlier_mask"] and not fused:
                 fm.find_inliers_batch(eprobs_na, 0.8, loss=cfg["loss"], ctx=ctx, out=act_e)
-            fm.refine_batch(eprobs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
-                            ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=eres)
+            fm.refine_batch(eprobs_gn if fused else eprobs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                            ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=eres,
+                            inlier_threshold=0.8 if fused else None)
             eres_host.copy_(eres, non_blocking=True)
 
         for _ in range(2):
@@ -511,6 +532,73 @@ def main():
                        "note": "HWC fp32 maps + descriptors + points in pinned host memory -> H2D -> find_inliers + "
                                "refine kernels -> result records D2H, all inside the timed region (PCIe-bound; cutting the step into "
                                "chunks whose uploads overlap the kernels measured 5 % slower and was dropped)"}
+        # ---- the same call with the maps LEFT in pinned host memory (zero-copy): the kernels fetch the rows they
+        # gather over PCIe themselves, and with record reuse that is about one evaluation's worth of rows instead
+        # of three whole maps.  Variant "maps": F, Gx, Gy stay on the host, descriptors + points are uploaded;
+        # variant "all": the descriptors stay on the host as well.
+        if not args.no_zero_copy:
+            _, nsup0 = fm.compute_cost_batch(eprobs_na, ctx=ctx)  # supported points at the initial pose (byte count only)
+            nsup0 = nsup0.cpu().numpy().astype(np.float64)
+            zc = {}
+            for variant in ("maps", "all"):
+                ref_of = (lambda i: devbuf[i]["ref"]) if variant == "maps" else (lambda i: host[i]["ref"])
+                zprobs = fm.ProblemBatch([fm.Problem(host[i]["F"], host[i]["Gx"], host[i]["Gy"], ref_of(i), devbuf[i]["pts3D"],
+                                                     scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024,
+                                                     active=act_e[i] if act_e is not None else None) for i in range(E)])
+                zprobs_gn = fm.ProblemBatch([fm.Problem(host[i]["F"], host[i]["Gx"], host[i]["Gy"], ref_of(i), devbuf[i]["pts3D"],
+                                                        scenes[i].K, scenes[i].R0, scenes[i].t0, 1024, 1024) for i in range(E)])
+                zprobs_na = fm.ProblemBatch([fm.Problem(host[i]["F"], None, None, ref_of(i), devbuf[i]["pts3D"], scenes[i].K,
+                                                        scenes[i].R0, scenes[i].t0, 1024, 1024) for i in range(E)])
+                up = ("pts3D", "ref") if variant == "maps" else ("pts3D",)
+
+                def zc_step():
+                    for i in range(E):
+                        for k in up:
+                            devbuf[i][k].copy_(host[i][k], non_blocking=True)
+                    if cfg["inlier_mask"] and not fused:
+                        fm.find_inliers_batch(zprobs_na, 0.8, loss=cfg["loss"], ctx=ctx, out=act_e)
+                    fm.refine_batch(zprobs_gn if fused else zprobs, cfg["n_iters"], loss=cfg["loss"], lambda_=cfg["lambda_"],
+                                    ratio_threshold=cfg["ratio_threshold"], levels=levels, ctx=ctx, sync=False, out=eres,
+                                    inlier_threshold=0.8 if fused else None)
+                    eres_host.copy_(eres, non_blocking=True)
+
+                for _ in range(2):
+                    zc_step()
+                torch.cuda.synchronize()
+                if world > 1:
+                    dist.barrier()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(ksteps):
+                    zc_step()
+                b.record()
+                torch.cuda.synchronize()
+                z_ms = a.elapsed_time(b)
+                if world > 1:
+                    tm = torch.tensor([z_ms], dtype=torch.float64, device=dev)
+                    dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+                    z_ms = float(tm.item())
+                zres = eres_host.numpy().view(RESULT_DTYPE).reshape(E)
+                same = all(np.ascontiguousarray(zres[f]).tobytes() == np.ascontiguousarray(res[:E][f]).tobytes()
+                           for f in ("R", "t", "best_cost", "best_num_inliers", "status"))
+                host_maps = 3 if variant == "maps" else 4          # of the 4 rows of a gather, those that cross PCIe
+                pcie = float(zres["gathered_rows"].astype(np.float64).sum()) * 4.0 * host_maps / 4.0
+                if cfg["inlier_mask"] and not fused:  # (fused: the pass's rows are in gathered_rows already)
+                    pcie += float(nsup0.sum()) * args.channels * 4.0 * (1 if variant == "maps" else 2)
+                pcie += sum(host[i][k].numel() * host[i][k].element_size() for i in range(E) for k in up)
+                zc[variant] = {"value": world * E * ksteps / (z_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(pcie),
+                               "d2h_bytes_per_step": int(d2h), "h2d_gbs": pcie * ksteps / (z_ms / 1e3) / 1e9,
+                               "results_equal_to_resident_run": bool(same)}
+            best = max(zc, key=lambda k: zc[k]["value"])
+            line["e2e_full_upload"] = line["e2e"]
+            line["e2e"] = dict(zc[best], queries_per_step=E, steps=ksteps, variant=best,
+                               note="same C ABI, inputs in pinned HOST memory, results back in host memory, all inside "
+                                    "the timed region.  The maps are not uploaded: pinned memory is mapped into the "
+                                    "device's address space and the kernels read the rows they gather over PCIe "
+                                    "(h2d_bytes_per_step = rows read + the uploaded arrays, counted from the kernels' "
+                                    "row counters); `e2e_full_upload` is the same step with every input copied to HBM "
+                                    "first, `e2e_zero_copy` has both variants")
+            line["e2e_zero_copy"] = zc
         del host, devbuf
 
         # ---- e2e one level up (the reference's feature_pnp): hypercolumns in pinned host memory -> H2D ->

@@ -30,6 +30,7 @@ struct fmpnp_ctx {
     // per-CTA scratch
     double* d_rec = nullptr;
     uint8_t* d_supp = nullptr;
+    uint8_t* d_inl = nullptr;   // inlier masks of the fused find_inliers pass
     size_t cap_points = 0;
     unsigned int* d_counter = nullptr;
     // geometry (overridable through the environment for tuning)
@@ -151,11 +152,14 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
     if (need > ctx->cap_points) {
         if (ctx->d_rec) FMPNP_CUDA(ctx, cudaFree(ctx->d_rec));
         if (ctx->d_supp) FMPNP_CUDA(ctx, cudaFree(ctx->d_supp));
+        if (ctx->d_inl) FMPNP_CUDA(ctx, cudaFree(ctx->d_inl));
         ctx->d_rec = nullptr;
         ctx->d_supp = nullptr;
+        ctx->d_inl = nullptr;
         ctx->cap_points = 0;
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_rec, need * kRecDoubles * sizeof(double)));
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_supp, need));
+        FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_inl, need));
         // no record tag of the new buffer may look like a generation that is handed out later
         FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_rec, 0, need * kRecDoubles * sizeof(double), stream));
         ctx->cap_points = need;
@@ -262,6 +266,7 @@ void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, con
     lp.B = B;
     lp.rec = ctx->d_rec;
     lp.supp = ctx->d_supp;
+    lp.inl = ctx->d_inl;
     lp.n_max = n_max;
     lp.work_counter = ctx->d_counter;
     lp.ring_per_warp = g.ring_per_warp;
@@ -367,6 +372,7 @@ int fmpnp_destroy(fmpnp_ctx* ctx) {
         if (ctx->h_queries[i]) cudaFreeHost(ctx->h_queries[i]);
     if (ctx->d_rec) cudaFree(ctx->d_rec);
     if (ctx->d_supp) cudaFree(ctx->d_supp);
+    if (ctx->d_inl) cudaFree(ctx->d_inl);
     if (ctx->d_counter) cudaFree(ctx->d_counter);
     if (ctx->d_states) cudaFree(ctx->d_states);
     if (ctx->d_part) cudaFree(ctx->d_part);
@@ -443,6 +449,8 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     lp.solver = o->solver;
     lp.results = results;
     lp.reuse = (ctx->reuse != 0 && o->gather_every_row == 0) ? 1 : 0;
+    lp.inlier_on = (o->inlier_threshold == o->inlier_threshold && o->inlier_threshold != 0.0) ? 1 : 0;  // 0 / NaN = off
+    lp.inlier_thr = o->inlier_threshold;
     {  // one generation per (query, level) of this launch; generations are never handed out twice
         const uint64_t gens = (uint64_t)B * (uint64_t)levels_eff;
         if (ctx->reuse_next + gens >= (1ull << 32)) {

@@ -59,6 +59,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
     rp.cpar = 0;
     double* rec = p.rec + (size_t)blockIdx.x * p.n_max * kRecDoubles;
     uint8_t* supp = p.supp + (size_t)blockIdx.x * p.n_max;
+    uint8_t* inl = p.inl ? p.inl + (size_t)blockIdx.x * p.n_max : nullptr;
 
     for (;;) {
         __syncthreads();
@@ -89,6 +90,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.part_out = nullptr;
         c.limit_given = false;
         c.reuse_gen = 0u;
+        c.active = q.active;
         {
             c.nranges = ranges_of(q.N);
             const int per = max(1, (q.N + c.nranges - 1) / c.nranges);
@@ -152,6 +154,29 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
             for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) sh.level_status[i] = 0;
         }
         __syncthreads();
+        if (p.inlier_on) {
+            // fused find_inliers (model.py:131-152) at (R0, t0): the points it keeps are the ones refined
+            // (optimize_feature_pnp.py:42-46).  Without a pyramid the pass streams all four rows and leaves
+            // tagged records, so the i == 0 evaluation below gathers nothing.
+            const bool share = p.n_levels == 0 && p.reuse;
+            c.c0 = 0;
+            c.Cl = q.C;
+            c.aligned = slice_aligned(q, 0, q.C, share);
+            c.loss_id = p.loss_id;
+            c.alpha = p.alpha;
+            c.ratio_mode = 1;
+            c.thr = p.inlier_thr;
+            c.inl_out = inl;
+            c.reuse_gen = share ? p.reuse_base + (uint32_t)qi : 0u;  // level 0 of this query (one level)
+            if (share)
+                evaluate<true, false, false>(c, sh.R, sh.t, sh, rp);
+            else
+                evaluate<false, false, false>(c, sh.R, sh.t, sh, rp);
+            __syncthreads();
+            c.inl_out = nullptr;
+            c.reuse_gen = 0u;
+            c.active = inl;
+        }
         bool run_levels = true;
         if (p.n_levels > 0) {
             // multilevel_optimization: initial_cost_ = compute_cost(...) on ALL channels (model.py:182)
@@ -465,7 +490,9 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         g.level = 0;
         g.it = 0;
         if (MODE == kModeRefine) p.results[q].status = FMPNP_STATUS_INCOMPLETE;
-        if (MODE == kModeComputeCost)
+        if (MODE == kModeRefine && p.inlier_on)  // fused find_inliers first (streams all four rows when its records are reused)
+            describe_evaluation(g, qd.R0, qd.t0, kPhaseInliers, (p.n_levels == 0 && p.reuse) ? 1 : 0, 0, qd.C, 1, p.loss_id, -1, uq);
+        else if (MODE == kModeComputeCost)
             describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, uq);
         else if (MODE == kModeFindInliers)
             describe_evaluation(g, qd.R0, qd.t0, kPhaseCost, 0, 0, qd.C, 1, p.loss_id, -1, uq);
@@ -512,14 +539,24 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.loss_id = gv.ev_loss;
         c.alpha = p.alpha;
         c.ratio_mode = gv.ev_ratio_mode;
+        c.inl_out = MODE == kModeFindInliers ? p.inliers_out + (size_t)qi * p.inliers_stride : nullptr;
+        c.active = q.active;
         c.thr = p.ratio_thr;
-        const bool grad = gv.ev_grad != 0;
+        if (MODE == kModeRefine && p.inlier_on) {  // fused find_inliers: its pass writes the mask every later evaluation reads
+            uint8_t* const inl = p.inl + (size_t)qi * p.n_max;
+            if (gv.phase == kPhaseInliers) {
+                c.inl_out = inl;
+                c.thr = p.inlier_thr;
+            } else {
+                c.active = inl;
+            }
+        }
+        const bool grad = gv.ev_grad != 0;             // rows streamed (the per-point phase of the inlier pass builds no normal equations)
         const int hist_entry = gv.ev_hist;
         c.reuse_gen = (MODE == kModeRefine && p.reuse && grad)
                           ? p.reuse_base + (uint32_t)(qi * (p.n_levels > 0 ? p.n_levels : 1) + gv.level)
                           : 0u;
         c.aligned = slice_aligned(q, c.c0, c.Cl, grad);
-        c.inl_out = MODE == kModeFindInliers ? p.inliers_out + (size_t)qi * p.inliers_stride : nullptr;
         c.h_px = nullptr;
         c.h_mask = nullptr;
         c.h_kept = nullptr;
@@ -570,7 +607,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             c.crank = u;
             c.part_out = parts + u * kPartStride;
             c.limit_given = ratio;
-            if (grad)
+            if (grad && !(MODE == kModeRefine && c.inl_out != nullptr))
                 reduce_points<true>(c, evpose, evpose + 9, sh, rp);
             else
                 reduce_points<false>(c, evpose, evpose + 9, sh, rp);
@@ -610,12 +647,12 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         __syncthreads();
         if (multi)
             combine_parts(sh, parts, uq);
-        else if (grad)
+        else if (grad && !(MODE == kModeRefine && c.inl_out != nullptr))
             reduce_points<true>(c, evpose, evpose + 9, sh, rp);
         else
             reduce_points<false>(c, evpose, evpose + 9, sh, rp);
         if (tid == 0) {
-            sh.n_evals += 1;
+            if (!(MODE == kModeRefine && c.inl_out != nullptr)) sh.n_evals += 1;  // the inlier pass is not an LM evaluation
             sh.gathered += (long long)sh.ev_ngath * c.Cl * (grad ? 4 : 2);
             sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (grad ? 4 : 2);
         }
@@ -624,7 +661,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         bool finished = false, have_eval = false;
         int lvl = gv.level, it = gv.it;
         const int phase = gv.phase;
-        enum { kStartLevel, kTryStep, kFinishLevel } next = kStartLevel;
+        enum { kStartLevel, kTryStep, kFinishLevel, kCostEval } next = kStartLevel;
 
         if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
             if (tid == 0) {
@@ -634,6 +671,9 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             finished = true;
         } else if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152): the mask was written by reduce_points
             finished = true;
+        } else if (phase == kPhaseInliers) {  // the mask is in `inl`: on to compute_cost (pyramid) or level 0
+            lvl = 0;
+            next = p.n_levels > 0 ? kCostEval : kStartLevel;
         } else if (phase == kPhaseCost) {
             if (sh.ev_nsup == 0) {  // compute_cost is None -> return the initial pose (model.py:183-187)
                 if (tid == 0) sh.status = FMPNP_STATUS_NO_INITIAL_COST;
@@ -681,7 +721,11 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         const int nlev = p.n_levels > 0 ? p.n_levels : 1;
         while (!finished && !have_eval) {
             __syncthreads();
-            if (next == kStartLevel) {
+            if (next == kCostEval) {  // multilevel: compute_cost on ALL channels (model.py:182), on the inliers
+                if (tid == 0)
+                    describe_evaluation(g, sh.R, sh.t, kPhaseCost, 0, 0, q.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, uq);
+                have_eval = true;
+            } else if (next == kStartLevel) {
                 if (tid == 0) {
                     const int c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
                     const int Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;

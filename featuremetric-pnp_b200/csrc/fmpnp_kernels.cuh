@@ -49,7 +49,7 @@ struct HistoryDev {
 // global FIFO, the CTA that finishes the last unit of an evaluation reduces the per-point records,
 // advances the query's LM state machine and queues the units of its next evaluation.
 // ---------------------------------------------------------------------------------------------
-enum TaskPhase { kPhaseCost = 0, kPhaseFirst = 1, kPhaseTrial = 2 };
+enum TaskPhase { kPhaseCost = 0, kPhaseFirst = 1, kPhaseTrial = 2, kPhaseInliers = 3 };
 
 struct __align__(16) QueryState {
     double R[9], t[3];    // current pose (last accepted)
@@ -63,7 +63,7 @@ struct __align__(16) QueryState {
     int32_t best_n, has_best, status, flag, hist_len, n_evals, initial_set;
     int32_t level_status[FMPNP_MAX_LEVELS];
     int32_t phase, level, it;
-    int32_t ev_grad, ev_c0, ev_Cl, ev_ratio_mode, ev_loss, ev_hist;  // the evaluation in flight
+    int32_t ev_grad, ev_c0, ev_Cl, ev_ratio_mode, ev_loss, ev_hist;  // the evaluation in flight (ev_grad: rows streamed)
     int32_t pending;      // its units still running
     int32_t ev_round;     // 0: streaming round, 1: summing round of an evaluation with a ratio test
 };
@@ -100,6 +100,7 @@ struct LaunchParams {
     // per-CTA scratch
     double* rec;    // [grid][n_max][kRecDoubles]
     uint8_t* supp;  // [grid][n_max]
+    uint8_t* inl;   // [grid][n_max] inlier mask of the fused find_inliers pass (inlier_on)
     int32_t n_max;
     unsigned int* work_counter;
     // staging ring geometry (slot size / depth are derived per evaluation, see set_geometry)
@@ -114,6 +115,12 @@ struct LaunchParams {
     // rows are not gathered again.  A record carries the tag (generation << 32 | cell); the generation is unique
     // per (launch, query, level) -- reuse_base + query * levels + level -- so nothing stale can ever match.
     int32_t reuse;          // 0: gather every row at every evaluation
+    // Fused inlier selection (fmpnp_options.inlier_threshold): find_inliers (model.py:131-152) at (R0, t0) runs as
+    // the first evaluation of the launch and the refinement continues on the points it keeps -- one iteration of
+    // feature_pnp_multi's loop (optimize_feature_pnp.py:42-46) without a second launch, and (without a pyramid)
+    // without a second gather: the pass leaves full records that the i == 0 evaluation reuses.
+    int32_t inlier_on;
+    double inlier_thr;
     uint32_t reuse_base;    // first generation of this launch (never 0)
 };
 

@@ -5,15 +5,16 @@
 
 namespace fmpnp {
 
-template <bool GRAD>
+// GRAD: rows streamed (F, Gx, Gy, ref or F, ref); RGRAD: whether the per-point phase builds the normal equations
+template <bool GRAD, bool RGRAD = GRAD, bool COUNT = true>
 __device__ __forceinline__ void evaluate(EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     set_geometry(c, GRAD ? 4 : 2);
     rp.pos = 0;  // the ring is empty between evaluations; its depth may change with the slice
     stream_points<GRAD>(c, R, t, sh, rp);
     __syncthreads();
-    reduce_points<GRAD>(c, R, t, sh, rp);
+    reduce_points<RGRAD>(c, R, t, sh, rp);
     if (threadIdx.x == 0) {
-        sh.n_evals += 1;
+        if (COUNT) sh.n_evals += 1;
         sh.gathered += (long long)sh.ev_ngath * c.Cl * (GRAD ? 4 : 2);
         sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (GRAD ? 4 : 2);
     }

@@ -58,6 +58,7 @@ struct EvalCtx {
     double thr;
     double* rec;           // per-point records of this CTA
     uint8_t* supp;         // per-point support flags of this CTA: 0 unsupported, 1 gathered, 2 record reused
+    const uint8_t* active; // points to leave out (0), or null: the caller's mask, or the fused find_inliers pass's
     uint32_t reuse_gen;    // generation of the record tags this evaluation may reuse (0 = gather every row)
     int32_t* h_px;         // history slices for the entry being evaluated (or null)
     uint8_t* h_mask;
@@ -126,7 +127,7 @@ __device__ __forceinline__ void acc1(float f, float r, float gx, float gy, doubl
 // projects point n, records support / history, returns the feature-map cell or -1
 __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const double* R, const double* t, int n) {
     const QueryDev& q = *c.q;
-    const bool act = (q.active == nullptr) || (q.active[n] != 0);
+    const bool act = (c.active == nullptr) || (__ldcg(c.active + n) != 0);  // .cg: may be another CTA's inlier mask
     const double x = q.pts[3 * n + 0], y = q.pts[3 * n + 1], z = q.pts[3 * n + 2];
     const Proj pr = project_point(R, t, q.K, x, y, z, q.im_w, q.im_h);
     const bool sup = act && pr.supported;

@@ -33,7 +33,8 @@ class COptions(C.Structure):
     _fields_ = [("n_iters", C.c_int32), ("loss_id", C.c_int32), ("barron_alpha", C.c_double),
                 ("lambda0", C.c_double), ("ratio_threshold", C.c_double), ("n_levels", C.c_int32),
                 ("levels", (C.c_int32 * 2) * MAX_LEVELS), ("solver", C.c_int32), ("cluster_size", C.c_int32),
-                ("gather_every_row", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("gather_every_row", C.c_int32), ("pad_", C.c_int32), ("inlier_threshold", C.c_double),
+                ("reserved", C.c_int32 * 2)]
 
 
 class CResult(C.Structure):
@@ -192,7 +193,10 @@ def loss_id_of(loss):
 
 
 class Problem:
-    """Device-resident inputs of one query (the product's layout: HWC fp32 maps)."""
+    """Inputs of one query (the product's layout: HWC fp32 maps).  Tensors live on the device -- or, for the maps
+    and the descriptors, in PINNED host memory (`tensor.pin_memory()`): pinned memory is mapped into the device's
+    address space, the kernels then read just the rows they gather over PCIe (zero-copy) instead of the caller
+    uploading whole maps first."""
 
     def __init__(self, F, Gx, Gy, ref, pts3D, K, R0, t0, im_width, im_height, active=None):
         self.F, self.Gx, self.Gy, self.ref, self.pts3D, self.active = F, Gx, Gy, ref, pts3D, active
@@ -205,8 +209,11 @@ class Problem:
                              ("active", active, torch.uint8)):
             if t_ is None:
                 continue
-            if not (isinstance(t_, torch.Tensor) and t_.is_cuda and t_.dtype == dt and t_.is_contiguous()):
-                raise FmpnpError("%s must be a contiguous CUDA %s tensor" % (name, dt))
+            ok = isinstance(t_, torch.Tensor) and t_.dtype == dt and t_.is_contiguous() and (
+                t_.is_cuda or (name in ("F", "Gx", "Gy", "ref") and t_.is_pinned()))
+            if not ok:
+                raise FmpnpError("%s must be a contiguous CUDA %s tensor%s" % (
+                    name, dt, " (or pinned host memory)" if name in ("F", "Gx", "Gy", "ref") else ""))
         if F.dim() != 3 or ref.dim() != 2 or pts3D.dim() != 2 or pts3D.shape[1] != 3:
             raise FmpnpError("expected F (Hf, Wf, C), ref (N, C), pts3D (N, 3)")
         self.Hf, self.Wf, self.C = (int(v) for v in F.shape)
@@ -236,18 +243,38 @@ class Problem:
         c.im_width, c.im_height = self.im_width, self.im_height
 
 
+class ProblemBatch:
+    """A list of problems with its fmpnp_problem array filled in once.  The batched calls accept it in place of the
+    list; a caller that refines the same queries repeatedly (or times the calls) then pays the marshalling of the
+    descriptors (about 4 us per problem in Python) once instead of per call."""
+
+    def __init__(self, problems):
+        self.problems = list(problems)
+        self.arr = (CProblem * len(self.problems))()
+        for i, p in enumerate(self.problems):
+            p.fill(self.arr[i])
+        self.n_max = max([p.N for p in self.problems] + [1])
+
+    def __len__(self):
+        return len(self.problems)
+
+    def __iter__(self):
+        return iter(self.problems)
+
+    def __getitem__(self, i):
+        return self.problems[i]
+
+
 def _problem_array(problems):
-    arr = (CProblem * len(problems))()
-    for i, p in enumerate(problems):
-        p.fill(arr[i])
-    return arr
+    return problems.arr if isinstance(problems, ProblemBatch) else ProblemBatch(problems).arr
 
 
 def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None, cluster_size=0,
-             gather_every_row=False):
+             gather_every_row=False, inlier_threshold=None):
     o = COptions()
     o.cluster_size = int(cluster_size)
     o.gather_every_row = 1 if gather_every_row else 0
+    o.inlier_threshold = 0.0 if inlier_threshold is None else float(inlier_threshold)
     lid, alpha = loss_id_of(loss)
     if barron_alpha is not None:
         alpha = float(barron_alpha)
@@ -270,11 +297,13 @@ def _stream_ptr():
 
 def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_threshold=None, levels=None,
                  track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None, cluster_size=0,
-                 gather_every_row=False):
+                 gather_every_row=False, inlier_threshold=None):
     """Batched sparseFeaturePnP.forward (levels=None) / multilevel_optimization (levels=[(s, e), ...]).
 
     gather_every_row=True reads the rows of every supported point at every evaluation; the default keeps the
     record of a point that stays in its feature-map cell (bit-identical results, see include/fmpnp.h).
+    inlier_threshold=t starts the launch with find_inliers(threshold=t, loss_fn=loss) at the initial pose and
+    refines the points it keeps (== find_inliers_batch + refine_batch with that mask as `active`, one launch).
 
     Returns a dict: `results` (numpy structured array, one fmpnp_result per query, on the host if
     sync else None), `results_dev` (raw device tensor), and with track=True `history` (dict of
@@ -282,7 +311,8 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     ctx = ctx or default_context()
     B = len(problems)
     dev = torch.device("cuda", ctx.device)
-    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size, gather_every_row)
+    o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size, gather_every_row,
+                 inlier_threshold)
     arr = _problem_array(problems)
     res_dev = out if out is not None else torch.empty((max(B, 1), RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
     hist, hbuf = None, None

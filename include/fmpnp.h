@@ -14,6 +14,10 @@
  *     throws; `fmpnp_last_error()` gives the text of the last failure on that context;
  *   - pointers documented "device" are CUDA device pointers on the context's device; the caller
  *     owns every buffer it passes; the library owns only the workspace inside `fmpnp_ctx`;
+ *     fmpnp_problem.F / Gx / Gy / ref may instead point to PINNED HOST memory that is mapped into
+ *     the device's address space (cudaHostAlloc / cudaHostRegister; with unified addressing the
+ *     host pointer is the device pointer): the kernels then fetch only the rows they gather over
+ *     PCIe ("zero-copy") and the caller does not upload whole maps;
  *   - launches are asynchronous on the `stream` argument (a `cudaStream_t` passed as void*);
  *     a context must not be used from two host threads at once;
  *   - there is NO CPU fallback: without a CUDA device fmpnp_create() fails.
@@ -114,7 +118,15 @@ typedef struct {
                                model.py:74-97), so the record is a function of (point, cell, channel slice) and
                                the result is bit-identical; its rows are not read again.  1: gather the rows of
                                every supported point at every evaluation (4 N C 4 bytes per iteration) */
-    int32_t reserved[5];
+    int32_t pad_;
+    double inlier_threshold;  /* 0 or NaN = off.  Otherwise the launch starts with find_inliers(pts3D, R_init, t_init,
+                               ..., threshold = inlier_threshold, loss_fn = loss_id) (model.py:131-152) over the
+                               active points and refines pts3D[inliers], feature_ref[inliers]: one round of
+                               feature_pnp_multi's loop (optimize_feature_pnp.py:42-46) in a single launch.  Same
+                               results as fmpnp_find_inliers_batch followed by fmpnp_refine_batch with its mask as
+                               `active`; without a pyramid the pass's records serve the first evaluation, so the
+                               rows are gathered once instead of twice */
+    int32_t reserved[2];
 } fmpnp_options;
 
 /* What the callers read back (sparse_to_dense_predictor.py:257): the returned pose,

@@ -318,6 +318,66 @@ def test_active_mask_equals_compaction(route):
     compare("active-mask", out["results"][0], out["history"], o, use_ratio=True, sel=sel)
 
 
+@pytest.mark.parametrize("cfg", [dict(C=16, levels=None, ratio=0.8, loss="squared_loss", lam=0.0),
+                                 dict(C=64, levels=None, ratio=None, loss="geman_mcclure_loss", lam=0.01),
+                                 dict(C=64, levels=[(32, 64), (8, 32), (0, 8)], ratio=0.9, loss="cauchy_loss", lam=0.01),
+                                 dict(C=7, levels=None, ratio=None, loss="huber_loss", lam=0.01)])
+def test_fused_inlier_pass_equals_two_calls(cfg, route):
+    """fmpnp_options.inlier_threshold == fmpnp_find_inliers_batch + fmpnp_refine_batch(active = its mask): the body of
+    feature_pnp_multi's loop (optimize_feature_pnp.py:42-46) in one launch; every result field and history entry
+    has the same bits (only the row counters differ: the fused pass gathers once), and the oracle agrees."""
+    Ns = [150, 37, 300, 64, 211, 1]
+    scs = [synth().make_scene(560 + i, N=n, C=cfg["C"], grad_scale=1.0 / 64, outlier_frac=0.2, **SMALL) for i, n in enumerate(Ns)]
+    kw = dict(loss=cfg["loss"], lambda_=cfg["lam"], ratio_threshold=cfg["ratio"], levels=cfg["levels"], track=True)
+    inl = fm().find_inliers_batch([to_problem(sc) for sc in scs], 0.8, loss=cfg["loss"]).cpu().numpy()
+    two = fm().refine_batch([to_problem(sc, active=inl[i, :Ns[i]]) for i, sc in enumerate(scs)], 6, **kw)
+    for sub_ in (slice(0, 6), slice(0, 1)):  # a batch (task scheduler) and a single query
+        probs = [to_problem(sc) for sc in scs[sub_]]
+        one = fm().refine_batch(probs, 6, inlier_threshold=0.8, **kw)
+        B = len(probs)
+        assert same_records(one["results"], two["results"][sub_], skip=("gathered_rows", "reused_rows"))
+        for b in range(B):
+            n = int(one["history"]["len"][b])
+            assert n == int(two["history"]["len"][b])
+            for k in ("Rs", "ts", "costs", "points2d", "mask", "kept"):
+                x, y = one["history"][k][b, :n], two["history"][k][b, :n]
+                if k in ("points2d", "mask", "kept"):  # per-point arrays are padded to the longest query of their batch
+                    x, y = x[:, :Ns[b]], y[:, :Ns[b]]
+                assert np.array_equal(x, y, equal_nan=k in ("Rs", "ts", "costs")), k
+        if cfg["levels"] is None:  # the pass's records serve the first evaluation: fewer rows than the two calls' refinement
+            assert (one["results"]["gathered_rows"] + one["results"]["reused_rows"] >=
+                    two["results"]["gathered_rows"][sub_] + two["results"]["reused_rows"][sub_]).all()
+        every = fm().refine_batch(probs, 6, inlier_threshold=0.8, gather_every_row=True, **kw)
+        assert same_records(one["results"], every["results"], skip=("gathered_rows", "reused_rows"))
+        clus = fm().refine_batch(probs[:1], 6, inlier_threshold=0.8, cluster_size=4, **kw)
+        assert same_records(clus["results"][0], one["results"][0])
+    sc = scs[0]
+    sel = np.nonzero(inl[0, :Ns[0]])[0]
+    assert 0 < len(sel) < Ns[0]
+    o = run_oracle(sc, 6, cfg["loss"], cfg["lam"], cfg["ratio"], cfg["levels"], sel=sel)
+    compare("fused-inliers", one["results"][0], one["history"], o, use_ratio=cfg["ratio"] is not None, sel=sel)
+
+
+def test_maps_in_pinned_host_memory_give_the_same_records():
+    """fmpnp_problem.F / Gx / Gy / ref may live in pinned (mapped) host memory: the kernels read the rows they gather
+    over PCIe.  Same bits as with device-resident maps."""
+    scs = [synth().make_scene(580 + i, N=n, C=64, grad_scale=1.0 / 64, outlier_frac=0.1, **SMALL) for i, n in enumerate([200, 90, 33, 150, 64, 7])]
+    kw = dict(loss="geman_mcclure_loss", lambda_=0.01, levels=[(32, 64), (0, 32)], track=True)
+    dev = fm().refine_batch([to_problem(sc) for sc in scs], 5, **kw)
+    pin = lambda t: t.cpu().pin_memory()
+    probs = [fm().Problem(pin(sc.F), pin(sc.Gx), pin(sc.Gy), pin(sc.ref), sc.pts3D.cuda(), sc.K, sc.R0, sc.t0,
+                          sc.im_width, sc.im_height) for sc in scs]
+    zc = fm().refine_batch(probs, 5, **kw)
+    assert same_records(zc["results"], dev["results"])
+    assert np.array_equal(zc["history"]["costs"], dev["history"]["costs"], equal_nan=True)
+    inl_d = fm().find_inliers_batch([to_problem(sc) for sc in scs], 0.8)
+    inl_z = fm().find_inliers_batch(probs, 0.8)
+    assert torch.equal(inl_d, inl_z)
+    with pytest.raises(fm().FmpnpError):  # pageable host memory is not reachable from the device
+        fm().Problem(scs[0].F.cpu(), pin(scs[0].Gx), pin(scs[0].Gy), pin(scs[0].ref), scs[0].pts3D.cuda(), scs[0].K,
+                     scs[0].R0, scs[0].t0, scs[0].im_width, scs[0].im_height)
+
+
 def test_unaligned_views_take_the_generic_path(route):
     """Descriptor / map tensors whose base address is not 16-byte aligned (a slice of a larger buffer)."""
     sc = synth().make_scene(57, N=64, C=16, grad_scale=1.0 / 64, **SMALL)
