@@ -347,6 +347,7 @@ def main():
     total_ms = start.elapsed_time(end)
     kern_ms = [a.elapsed_time(b) for a, b in kev]
     launches = ctx.launches - launches0
+    geo = ctx.last_geometry  # of the timed refinement launches
     if world > 1:
         tmax = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -379,7 +380,6 @@ def main():
         except Exception:
             traffic = None
     nominal = (args.iters + 1) * 4 * args.points * 4 * args.channels * B
-    geo = ctx.last_geometry
     kname = "fmpnp::refine_tasks_kernel" if geo["tasks_per_evaluation"] else "fmpnp::refine_kernel"
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "kernel_ms": k_ms,

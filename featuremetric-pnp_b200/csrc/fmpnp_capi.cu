@@ -187,7 +187,7 @@ int32_t max_points(const fmpnp_problem* probs, int32_t B) {
     return n_max;
 }
 
-int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g) {
+int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g, bool reuse = false) {
     int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
     int S = requested_cluster > 0 ? requested_cluster : ctx->cluster;
     // Task scheduler (default): an evaluation is cut into U tasks so that about three tasks per CTA slot are
@@ -202,7 +202,9 @@ int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Ge
         U = ctx->units;
         if (U <= 0) {
             U = 1;  // ... with at least 64 points per task, or 32 when the tasks would not even fill the CTA slots
-            while (U < kRanges && (int64_t)B * U < 3 * 2 * (int64_t)ctx->sm_count && (int64_t)n_max >= 128 * (int64_t)U) U *= 2;
+            // (with record reuse most evaluations gather next to nothing and pay per task: half as many, larger tasks)
+            const int64_t per_slot_x2 = reuse ? 3 : 6;  // tasks wanted per CTA slot, times two
+            while (U < kRanges && (int64_t)B * U * 2 < per_slot_x2 * 2 * (int64_t)ctx->sm_count && (int64_t)n_max >= 128 * (int64_t)U) U *= 2;
             while (U < kRanges && (int64_t)B * U < 2 * (int64_t)ctx->sm_count && (int64_t)n_max >= 64 * (int64_t)U) U *= 2;
         }
         if (U < 1 || U > kRanges || (U & (U - 1)) != 0)
@@ -421,7 +423,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     Geometry g;
-    int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g);
+    int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g, ctx->reuse != 0 && o->gather_every_row == 0);
     if (rc) return rc;
     int32_t n_max;
     rc = stage(ctx, probs, B, g.units > 0 ? B : g.grid, &n_max, stream);

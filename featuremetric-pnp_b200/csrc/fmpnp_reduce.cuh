@@ -140,14 +140,25 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
 #pragma unroll
             for (int i = 0; i < 28; ++i) acc[i] = 0.0;
             for (int n = r0 + lane; n < r1; n += 32) {
+                // flag, record and point are loaded side by side (their addresses depend on n only): one L2 round
+                // trip per point instead of three; what an unsupported point's record holds is never used
                 const uint8_t sflag = __ldcg(c.supp + n);
+                const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+                const double2 rc0 = __ldcg(r);
+                double2 rc1 = make_double2(0.0, 0.0), rc2 = rc1;
+                double ptx = 0.0, pty = 0.0, ptz = 0.0;
+                if (GRAD) {
+                    rc1 = __ldcg(r + 1);
+                    rc2 = __ldcg(r + 2);
+                    ptx = q.pts[3 * n];
+                    pty = q.pts[3 * n + 1];
+                    ptz = q.pts[3 * n + 2];
+                }
                 const bool sup = sflag != 0;
                 bool keep = false;
                 if (sup) {
                     ++cnt[1];
                     cnt[2] += sflag == 1;
-                    const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
-                    const double2 rc0 = __ldcg(r);
                     const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
                     double rho = x, w = 1.0;
                     if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
@@ -156,9 +167,7 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
                         ++cnt[0];
                         acc[27] = __dadd_rn(acc[27], rho);
                         if (GRAD) {
-                            const double2 rc1 = __ldcg(r + 1), rc2 = __ldcg(r + 2);
-                            const Proj pr = project_point(R, t, q.K, q.pts[3 * n], q.pts[3 * n + 1], q.pts[3 * n + 2],
-                                                          q.im_w, q.im_h);
+                            const Proj pr = project_point(R, t, q.K, ptx, pty, ptz, q.im_w, q.im_h);
                             contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
                         }
                     }

@@ -128,6 +128,10 @@ __device__ __forceinline__ void acc1(float f, float r, float gx, float gy, doubl
 __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const double* R, const double* t, int n) {
     const QueryDev& q = *c.q;
     const bool act = (c.active == nullptr) || (__ldcg(c.active + n) != 0);  // .cg: may be another CTA's inlier mask
+    // the record's tag does not depend on the projection: its load travels with the point's (one L2 round trip, not two)
+    long long* const tag = reinterpret_cast<long long*>(c.rec + (size_t)n * kRecDoubles + kRecTagSlot);
+    long long have = 0;
+    if (c.reuse_gen != 0u) have = __ldcg(tag);  // .cg: another CTA may have written it (task scheduler)
     const double x = q.pts[3 * n + 0], y = q.pts[3 * n + 1], z = q.pts[3 * n + 2];
     const Proj pr = project_point(R, t, q.K, x, y, z, q.im_w, q.im_h);
     const bool sup = act && pr.supported;
@@ -140,10 +144,9 @@ __device__ __forceinline__ int32_t project_and_flag(const EvalCtx& c, const doub
     uint8_t flag = sup ? 1 : 0;
     if (c.reuse_gen != 0u && sup) {
         // nearest-cell lookup (model.py:74-97): same cell, same slice => same rows => the record the point already
-        // has is the one this evaluation would compute.  .cg: another CTA may have written it (task scheduler).
-        long long* tag = reinterpret_cast<long long*>(c.rec + (size_t)n * kRecDoubles + kRecTagSlot);
+        // has is the one this evaluation would compute.
         const long long want = (long long)(((unsigned long long)c.reuse_gen << 32) | (unsigned int)cell);
-        if (__ldcg(tag) == want) {
+        if (have == want) {
             flag = 2;
             cell = -1;  // nothing to gather
         } else {

@@ -206,7 +206,12 @@ def test_automatic_geometry_and_batch_size_independence():
         g = ctx.last_geometry
         U = g["tasks_per_evaluation"]
         assert g["cluster_size"] == 1 and U in (1, 2, 4, 8) and g["grid"] <= min(2 * sms, B * U), g
-        assert U >= 4 or B * U >= 6 * sms, g   # about three tasks per CTA slot; a task keeps >= 64 of the 500 points
+        # about 1.5 tasks per CTA slot with record reuse (light evaluations pay per task), 3 when every row is gathered
+        assert U >= 4 or B * U >= 3 * sms, g
+        full = fm().refine_batch(batch, 5, loss="geman_mcclure_loss", lambda_=0.01, gather_every_row=True)["results"]
+        U2 = ctx.last_geometry["tasks_per_evaluation"]
+        assert U2 >= U and (U2 >= 4 or B * U2 >= 6 * sms), (U, U2)  # a task keeps >= 64 of the 500 points
+        assert same_records(r, full, skip=("gathered_rows", "reused_rows"))
         if B >= 6 * sms:
             assert U == 1
         if B == 1:
