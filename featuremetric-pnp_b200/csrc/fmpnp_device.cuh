@@ -52,6 +52,14 @@ __device__ __forceinline__ Proj project_point(const double* __restrict__ R, cons
 // floor division exactly (the quotient is either an integer or at least 1/height away from one).
 __device__ __forceinline__ int32_t cell_index(int32_t px, int32_t py, int32_t Hf, int32_t Wf, int32_t im_w,
                                               int32_t im_h) {
+    // (called for supported points only: 0 <= px < im_w, 0 <= py < im_h.)  64-bit integer division is a ~90-instruction
+    // dependent chain on the GPU; the products fit 32 bits for every realistic size, and then a 32-bit division
+    // gives the same integers.  The test is uniform across a query.
+    if ((int64_t)im_h * Hf <= 0x7fffffffll && (int64_t)im_w * Wf <= 0x7fffffffll) {
+        const uint32_t row = ((uint32_t)py * (uint32_t)Hf) / (uint32_t)im_h;
+        const uint32_t col = ((uint32_t)px * (uint32_t)Wf) / (uint32_t)im_w;
+        return (int32_t)(row * (uint32_t)Wf + col);
+    }
     const int32_t row = (int32_t)(((int64_t)py * Hf) / im_h);
     const int32_t col = (int32_t)(((int64_t)px * Wf) / im_w);
     return row * Wf + col;
