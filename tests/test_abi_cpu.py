@@ -90,10 +90,14 @@ def test_header_is_plain_c_and_links_against_the_library(tmp_path):
     hdr = open(os.path.join(ROOT, "include", "fmpnp.h")).read()
     names = sorted(set(re.findall(r"\b(fmpnp_[a-z_]+)\s*\(", re.sub(r"/\*.*?\*/", "", hdr, flags=re.S))))
     src = tmp_path / "abi.c"
-    src.write_text('#include <stdio.h>\n#include "fmpnp.h"\n'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "fmpnp.h"\n'
                    "typedef void (*fn_t)(void);\nint main(void) {\n  fn_t fns[] = {%s};\n"
                    '  printf("%%d %%d %%d %%d %%d %%d\\n", fmpnp_version(), fmpnp_struct_size(0), fmpnp_struct_size(1),\n'
                    "         fmpnp_struct_size(2), (int)sizeof(fmpnp_problem), (int)(sizeof(fns) / sizeof(fns[0])));\n"
+                   '  printf("%%d %%d %%d %%d %%d %%d\\n", (int)offsetof(fmpnp_options, gather_every_row),\n'
+                   "         (int)offsetof(fmpnp_options, inlier_threshold), (int)sizeof(fmpnp_options),\n"
+                   "         (int)offsetof(fmpnp_result, gathered_rows), (int)offsetof(fmpnp_result, reused_rows),\n"
+                   "         (int)sizeof(fmpnp_result));\n"
                    "  return 0;\n}\n" % ", ".join("(fn_t)%s" % n for n in names))
     exe = tmp_path / "abi"
     libdir = os.path.dirname(fm.lib_path())
@@ -101,3 +105,30 @@ def test_header_is_plain_c_and_links_against_the_library(tmp_path):
                     str(src), "-o", str(exe), "-L", libdir, "-lfmpnp", "-Wl,-rpath," + libdir], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
     assert int(out[0]) == 101 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)
+    # the ctypes mirrors place the fields added in version 101 where the C compiler does
+    from fmpnp_b200 import binding as b
+    import ctypes
+    assert [int(v) for v in out[6:12]] == [b.COptions.gather_every_row.offset, b.COptions.inlier_threshold.offset,
+                                           ctypes.sizeof(b.COptions), b.CResult.gathered_rows.offset,
+                                           b.CResult.reused_rows.offset, ctypes.sizeof(b.CResult)]
+
+
+def test_problem_batch_marshals_once():
+    """ProblemBatch fills the fmpnp_problem array at construction; the batched calls take its array as is."""
+    fm = _ensure_built()
+    from fmpnp_b200 import binding as b
+
+    class FakeProblem:  # what Problem.fill() needs, without CUDA tensors
+        N, C, Hf, Wf, im_width, im_height = 5, 8, 4, 4, 64, 64
+
+        def __init__(self, k):
+            self.k = k
+
+        def fill(self, c):
+            c.N, c.C, c.Hf, c.Wf, c.im_width, c.im_height = self.N + self.k, self.C, self.Hf, self.Wf, 64, 64
+            c.F = 0x1000 * (self.k + 1)
+
+    batch = fm.ProblemBatch([FakeProblem(k) for k in range(3)])
+    assert len(batch) == 3 and batch.n_max == 5 and batch[1].k == 1 and [p.k for p in batch] == [0, 1, 2]
+    assert b._problem_array(batch) is batch.arr and [batch.arr[i].N for i in range(3)] == [5, 6, 7]
+    assert batch.arr[2].F == 0x3000
