@@ -158,15 +158,17 @@ class sparseFeaturePnP(nn.Module):
         self.track_["threshold_mask"].append(threshold_mask)
 
     # -- shared tail of forward / multilevel_optimization ---------------------------------------
-    def _run(self, prob, levels, track, select=None):
+    def _run(self, prob, levels, track, select=None, inlier_threshold=None):
         """One query through torch.ops.fmpnp.refine_batch (PyTorch custom op -> C ABI -> CUDA kernel).
         `select`: boolean mask over the points; the history is reported for those points only (a
-        caller that passes pts3D[inliers] to the reference sees exactly these rows)."""
+        caller that passes pts3D[inliers] to the reference sees exactly these rows).
+        `inlier_threshold`: the launch starts with find_inliers(threshold, loss_fn=self.loss_fn) at the initial
+        pose and refines the points it keeps (fmpnp_options.inlier_threshold)."""
         loss_id, alpha = _fm.loss_id_of(self.loss_fn)
         rt = float("nan") if self.ratio_threshold_ is None else float(self.ratio_threshold_)
         solver = {"cholesky": 0, "lu": 1}[self.solver]
-        opts = torch.tensor([float(self.iterations), float(loss_id), alpha, float(self.lambda_), rt, float(solver)],
-                            dtype=torch.float64)
+        opts = torch.tensor([float(self.iterations), float(loss_id), alpha, float(self.lambda_), rt, float(solver),
+                             0.0 if inlier_threshold is None else float(inlier_threshold), 0.0], dtype=torch.float64)
         lv = torch.tensor(levels if levels else [], dtype=torch.int32).reshape(-1, 2)
         outs = torch.ops.fmpnp.refine_batch(
             [prob.F], [prob.Gx], [prob.Gy], [prob.ref], [prob.pts3D], torch.from_numpy(prob.K.reshape(1, 3, 3)),
@@ -267,9 +269,10 @@ class sparseFeaturePnP(nn.Module):
         self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
         return R, t
 
-    def forward_packed(self, prob, track=False, select=None):
-        """forward() on device-resident inputs (an fmpnp_b200.Problem)."""
-        R_out, t_out, r = self._run(prob, None, track, select)
+    def forward_packed(self, prob, track=False, select=None, inlier_threshold=None):
+        """forward() on device-resident inputs (an fmpnp_b200.Problem); with `inlier_threshold`, on the points
+        find_inliers(threshold, loss_fn=self.loss_fn) keeps at the initial pose (same launch)."""
+        R_out, t_out, r = self._run(prob, None, track, select, inlier_threshold)
         if self.initial_cost_ is None and int(r["best_num_inliers"]) >= 0:
             self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
         return R_out, t_out

@@ -83,7 +83,11 @@ def feature_pnp_multi(query_hypercolumns, reference_hypercolumns, prediction, K,
                       threshold=None, loss_fn=None):
     """Reference optimize_feature_pnp.py:20-47: three rounds of {refine on the current inliers, re-select
     inliers at the refined pose}.  `threshold` / `loss_fn` are forwarded to find_inliers when given (the
-    reference takes them from gin: `find_inliers.threshold = 0.8`)."""
+    reference takes them from gin: `find_inliers.threshold = 0.8`).
+
+    A selection and the refinement that follows it run as ONE launch (fmpnp_options.inlier_threshold) when the
+    mask itself is not needed on the host (track=False) and find_inliers uses the optimizer's loss; the
+    selection after the last round, whose result the reference discards, is not computed."""
     prob = build_problem(query_hypercolumns, reference_hypercolumns, prediction, K, image_shape)
     kw = {}
     if threshold is not None:
@@ -91,13 +95,15 @@ def feature_pnp_multi(query_hypercolumns, reference_hypercolumns, prediction, K,
     if loss_fn is not None:
         kw["loss_fn"] = loss_fn
 
-    def select(R, t):
-        p = _with(prob, R, t)
+    def selection_args():
         thr = kw.get("threshold", _gin_default(find_inliers, "threshold"))
         if thr is None:
             raise TypeError("find_inliers needs a threshold (gin: find_inliers.threshold = ...)")
-        loss = kw.get("loss_fn", _gin_default(find_inliers, "loss_fn") or "squared_loss")
-        return _fm.find_inliers_batch([p], float(thr), loss=loss)[0, :prob.N].contiguous()
+        return float(thr), kw.get("loss_fn", _gin_default(find_inliers, "loss_fn") or "squared_loss")
+
+    def select(R, t):
+        thr, loss = selection_args()
+        return _fm.find_inliers_batch([_with(prob, R, t)], thr, loss=loss)[0, :prob.N].contiguous()
 
     R, t = torch.from_numpy(prob.R0.reshape(3, 3).copy()), torch.from_numpy(prob.t0.copy())
     if getattr(prediction, "inlier_mask", None) is not None:
@@ -106,12 +112,18 @@ def feature_pnp_multi(query_hypercolumns, reference_hypercolumns, prediction, K,
         inliers = torch.from_numpy(m.astype(np.uint8)).to(prob.pts3D.device)
     else:
         print("No initial inliers found.")
-        inliers = select(R, t)
+        inliers = None  # selected at (R, t) by the first round
     model = sparseFeaturePnP()  # parameters from gin
     for _ in range(3):
+        if inliers is None:
+            thr, loss = selection_args()
+            if not track and _fm.loss_id_of(loss) == _fm.loss_id_of(model.loss_fn):
+                R, t = model.forward_packed(_with(prob, R, t), inlier_threshold=thr)  # selection + refinement, one launch
+                continue
+            inliers = select(R, t)
         R, t = model.forward_packed(_with(prob, R, t, active=inliers), track=track,
                                     select=inliers.bool().cpu().numpy() if track else None)
-        inliers = select(R, t)
+        inliers = None  # re-selected at the refined pose by the next round
     return R, t, model
 
 

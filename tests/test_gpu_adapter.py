@@ -171,6 +171,31 @@ def test_feature_pnp_multi_matches_reference_adapter(name, monkeypatch):
     assert np.abs(R.numpy() - g["out_R"]).max() < 1e-7 and np.abs(t.numpy() - g["out_t"]).max() < 1e-7
 
 
+@pytest.mark.parametrize("name", ["adapter_multi_mask", "adapter_multi_nomask"])
+def test_feature_pnp_multi_untracked_runs_selection_and_refinement_in_one_launch(name, monkeypatch):
+    """track=False: every {find_inliers, forward} pair of feature_pnp_multi is one launch
+    (fmpnp_options.inlier_threshold); same pose as the reference adapter's fixture and as the tracked path."""
+    import fmpnp_b200 as fm
+    import helpers.utils as hu
+    import model
+    from pose_prediction import optimize_feature_pnp as adapter
+    g = load(name)
+    monkeypatch.setattr(adapter, "sparseFeaturePnP", functools.partial(
+        model.sparseFeaturePnP, n_iters=int(g["n_iters"]), loss_fn=getattr(hu, g["loss"]), lambda_=float(g["lambda_"])))
+    args = (torch.from_numpy(g["qh"]).cuda(), torch.from_numpy(g["rh"]).cuda(), prediction_of(g), torch.from_numpy(g["K"]),
+            [int(v) for v in g["image_shape"]])
+    n0 = fm.default_context().launches
+    R, t, m = adapter.feature_pnp_multi(*args, track=False, threshold=float(g["threshold"]), loss_fn=getattr(hu, g["loss"]))
+    launches = fm.default_context().launches - n0
+    # build_problem: Sobel + pack, descriptor gather; then one launch per round (the first round of a prediction
+    # that brings its own inlier mask has nothing to select)
+    assert launches == 2 + 3, launches
+    assert np.abs(R.numpy() - g["out_R"]).max() < 1e-7 and np.abs(t.numpy() - g["out_t"]).max() < 1e-7
+    Rt, tt, mt = adapter.feature_pnp_multi(*args, track=True, threshold=float(g["threshold"]), loss_fn=getattr(hu, g["loss"]))
+    assert torch.equal(R, Rt) and torch.equal(t, tt) and m.best_num_inliers_ == mt.best_num_inliers_
+    assert float(m.best_cost_) == float(mt.best_cost_)
+
+
 def test_optimize_feature_pnp_entry_point(monkeypatch):
     """The top-level entry of the adapter: reference hypercolumn from `net`, (list(t), list(quaternion), model) out."""
     import helpers.utils as hu
