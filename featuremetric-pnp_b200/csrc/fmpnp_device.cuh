@@ -110,11 +110,16 @@ __device__ __forceinline__ void robust_loss(int loss_id, double alpha, double x,
 __device__ __forceinline__ void contract_point(double fx, double fy, double X, double Y, double Z, double w,
                                                double Sxx, double Sxy, double Syy, double bx, double by,
                                                double* __restrict__ acc) {
-    // J_px_p (model.py:377-382): [[fx, 0, -fx X / Z], [0, fy, -fy Y / Z]] / Z
-    const double j00 = fx / Z;
-    const double j02 = (__dmul_rn(-fx, X) / Z) / Z;
-    const double j11 = fy / Z;
-    const double j12 = (__dmul_rn(-fy, Y) / Z) / Z;
+    // J_px_p (model.py:377-382): [[fx, 0, -fx X / Z], [0, fy, -fy Y / Z]] / Z.  One division (1 / Z) and
+    // multiplications instead of the reference's six divisions: a float64 division is a ~30-instruction dependent
+    // chain, and this function runs for every supported point of every evaluation.  The entries differ from the
+    // quotients by at most 2 ulp -- the same size as the re-association of J = G A that this path has anyway; no
+    // integer (pixel index, mask) depends on them except through the pose, like on every other rounding of H, g.
+    const double rZ = 1.0 / Z;
+    const double j00 = __dmul_rn(fx, rZ);
+    const double j02 = __dmul_rn(__dmul_rn(__dmul_rn(-fx, X), rZ), rZ);
+    const double j11 = __dmul_rn(fy, rZ);
+    const double j12 = __dmul_rn(__dmul_rn(__dmul_rn(-fy, Y), rZ), rZ);
     // A = J_px_p [I | -skew(P)],  -skew(P) = [[0, Z, -Y], [-Z, 0, X], [Y, -X, 0]]
     double ax[6], ay[6];
     ax[0] = j00;  ax[1] = 0.0;  ax[2] = j02;
