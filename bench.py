@@ -390,7 +390,9 @@ def main():
                              "note": "the reference's lookup is nearest-cell (model.py:74-97): a point that projects "
                                      "into the same cell as at its previous evaluation keeps its record (bit-identical) "
                                      "and its rows are not read again; `achieved` counts the contract's algorithmic "
-                                     "bytes (4 rows per supported point per evaluation), `gathered` the bytes read"},
+                                     "bytes (4 rows per supported point per evaluation), `gathered` the bytes read.  "
+                                     "Nothing carries over from one step to the next: every launch tags its records "
+                                     "with fresh generations, so each timed step gathers its first evaluation in full"},
                 "nominal_bytes_per_launch": float(nominal) if levels is None else None,
                 "share_of_step": k_ms * args.steps / total_ms, "geometry": geo,
                 "kernel_ms_all": [round(x, 3) for x in kern_ms],
