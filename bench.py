@@ -386,7 +386,7 @@ def main():
                 "algorithmic_bytes_per_launch": alg_bytes, "inlier_pass_bytes_per_launch": pass_bytes,
                 "gathered": {"bytes_per_launch": gath_bytes, "gbs": gath_bytes / (k_ms / 1e3) / 1e9,
                              "frac_of_peak": gath_bytes / (k_ms / 1e3) / 1e9 / peak,
-                             "reused_fraction_of_rows": reused_bytes / max(alg_bytes, 1.0),
+                             "reused_fraction_of_rows": reused_bytes / max(gath_bytes + reused_bytes, 1.0),
                              "note": "the reference's lookup is nearest-cell (model.py:74-97): a point that projects "
                                      "into the same cell as at its previous evaluation keeps its record (bit-identical) "
                                      "and its rows are not read again; `achieved` counts the contract's algorithmic "

@@ -1,0 +1,64 @@
+"""bench.py's contract on a tiny workload: the reference arm (CPU, runs everywhere) and, on a GPU, our arm.
+
+The sizes are overridden on the command line (the defaults are BASELINE.json's configuration); what is checked is
+the shape of the JSON line the driver parses, not a number."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TINY = ["--queries", "6", "--points", "192", "--channels", "32", "--map", "16", "--iters", "4"]
+
+
+def run_bench(extra, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py")] + TINY + extra, capture_output=True, text=True,
+                       env=e, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    return [json.loads(l) for l in p.stdout.splitlines() if l.startswith("{")]
+
+
+def test_reference_arm_line_and_idle_ranks():
+    lines = run_bench(["--impl", "reference", "--steps", "1", "--warmup", "1"])
+    assert len(lines) == 1
+    d = lines[0]
+    assert d["impl"] == "reference" and d["unit"] == "queries/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["steps"] == 1 and d["scaling"] == "weak" and d["vs_baseline"] is None
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    assert d["e2e"] == {"value": d["value"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in d["config"] and "model" not in d["config"]
+    # under torchrun only rank 0 works and prints; the other ranks exit 0 without output
+    assert run_bench(["--impl", "reference", "--steps", "1", "--warmup", "0", "--gpus", "2"],
+                     env={"RANK": "1", "LOCAL_RANK": "1", "WORLD_SIZE": "2"}) == []
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("config", ["gn_inlier", "geman_lm", "pyramid"])
+def test_our_arm_line(config):
+    lines = run_bench(["--config", config, "--steps", "2", "--warmup", "3", "--e2e-queries", "3", "--cpu-queries", "2"])
+    assert len(lines) == 1
+    d = lines[0]
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "roofline", "clocks", "gpu_launches", "e2e", "cpu_baseline"):
+        assert k in d, k
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["data"] == "synthetic" and d["gpu_launches"] >= 2
+    r = d["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and r["peak"] > 0 and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    assert r["kernel"].startswith("fmpnp::refine") and 0 < r["share_of_step"] <= 1.001
+    g, e = r["gathered"], r["every_row_gathered"]
+    assert 0 <= g["reused_fraction_of_rows"] < 1 and g["bytes_per_launch"] > 0  # (the first evaluation always gathers)
+    assert e["results_bit_identical_to_default"] is True and e["bytes_per_launch"] >= g["bytes_per_launch"]
+    for k in ("e2e", "e2e_full_upload"):
+        assert d[k]["value"] > 0 and d[k]["h2d_bytes_per_step"] > 0 and d[k]["d2h_bytes_per_step"] > 0
+    assert d["e2e"]["results_equal_to_resident_run"] is True
+    assert all(v["results_equal_to_resident_run"] for v in d["e2e_zero_copy"].values())
+    if config != "pyramid":  # (a pyramid reads F and ref once more for compute_cost; on maps this small that can outweigh the upload)
+        assert d["e2e"]["h2d_bytes_per_step"] < d["e2e_full_upload"]["h2d_bytes_per_step"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["value"] > 0 and cb["cores"] >= 1
+    assert set(d["status_histogram"]) <= {"0", "1", "2", "3"}
