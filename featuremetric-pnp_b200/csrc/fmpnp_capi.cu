@@ -54,6 +54,11 @@ struct fmpnp_ctx {
     // record reuse: generations handed out so far (tags of `d_rec` hold generation << 32 | cell, never generation 0)
     uint64_t reuse_next = 1;
     int reuse = 1;  // FMPNP_REUSE=0: gather every row at every evaluation, whatever the options say
+    // One workspace per context: a call issued on another stream than the previous one waits for that call's
+    // kernels first (cudaStreamWaitEvent), so that two launches of a context never overlap on the device.
+    cudaEvent_t last_done = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool last_pending = false;
 };
 
 namespace {
@@ -92,6 +97,20 @@ int validate_problem(fmpnp_ctx* ctx, const fmpnp_problem& p, int b, bool need_gr
         return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: null F / ref / pts3D", b);
     if (need_grad && (!p.Gx || !p.Gy))
         return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "problem %d: null Gx / Gy", b);
+    return FMPNP_SUCCESS;
+}
+
+// The workspace (records, flags, states, queue, counters) belongs to the context, not to a stream: a call on a
+// different stream than the previous call's is ordered behind it on the device.  Same stream: already ordered.
+int order_after_previous(fmpnp_ctx* ctx, cudaStream_t stream) {
+    if (ctx->last_pending && stream != ctx->last_stream) FMPNP_CUDA(ctx, cudaStreamWaitEvent(stream, ctx->last_done, 0));
+    return FMPNP_SUCCESS;
+}
+
+int mark_launched(fmpnp_ctx* ctx, cudaStream_t stream) {
+    FMPNP_CUDA(ctx, cudaEventRecord(ctx->last_done, stream));
+    ctx->last_stream = stream;
+    ctx->last_pending = true;
     return FMPNP_SUCCESS;
 }
 
@@ -347,7 +366,8 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
         cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess ||
         cudaMalloc(&ctx->d_counter, sizeof(unsigned int)) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->staged[0], cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->staged[1], cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&ctx->staged[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->last_done, cudaEventDisableTiming) != cudaSuccess) {
         delete ctx;
         return FMPNP_ERR_CUDA;
     }
@@ -382,6 +402,7 @@ int fmpnp_destroy(fmpnp_ctx* ctx) {
     if (ctx->d_sched) cudaFree(ctx->d_sched);
     for (int i = 0; i < 2; ++i)
         if (ctx->staged[i]) cudaEventDestroy(ctx->staged[i]);
+    if (ctx->last_done) cudaEventDestroy(ctx->last_done);
     delete ctx;
     return FMPNP_SUCCESS;
 }
@@ -422,6 +443,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (int rc0 = order_after_previous(ctx, stream)) return rc0;
     Geometry g;
     int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g, ctx->reuse != 0 && o->gather_every_row == 0);
     if (rc) return rc;
@@ -477,6 +499,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     }
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
     FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
+    if (int rc1 = mark_launched(ctx, stream)) return rc1;
     ctx->launches += 1;
     ctx->last = {g.grid, g.cluster, g.ring_bytes, g.units};
     return FMPNP_SUCCESS;
@@ -493,6 +516,7 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (int rc0 = order_after_previous(ctx, stream)) return rc0;
     Geometry g;
     int rc = geometry(ctx, B, max_points(probs, B), 0, &g);
     if (rc) return rc;
@@ -510,6 +534,7 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     lp.nsup_out = n_supported;
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
     FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
+    if (int rc1 = mark_launched(ctx, stream)) return rc1;
     ctx->launches += 1;
     ctx->last = {g.grid, g.cluster, g.ring_bytes, g.units};
     return FMPNP_SUCCESS;
@@ -529,6 +554,7 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (int rc0 = order_after_previous(ctx, stream)) return rc0;
     Geometry g;
     int rc = geometry(ctx, B, max_points(probs, B), 0, &g);
     if (rc) return rc;
@@ -548,6 +574,7 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     lp.inliers_stride = n_stride;
     FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned int), stream));
     FMPNP_CUDA(ctx, launch_refine(lp, g.grid, g.ring_bytes, stream));
+    if (int rc1 = mark_launched(ctx, stream)) return rc1;
     ctx->launches += 1;
     ctx->last = {g.grid, g.cluster, g.ring_bytes, g.units};
     return FMPNP_SUCCESS;
@@ -608,6 +635,65 @@ int fmpnp_blur_chw(fmpnp_ctx* ctx, const void* src, int32_t src_is_f64, const do
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     FMPNP_CUDA(ctx, launch_blur_chw(src, src_is_f64, kernel, dst, C, H, W, k, pad, static_cast<cudaStream_t>(stream_)));
     ctx->launches += 1;
+    return FMPNP_SUCCESS;
+}
+
+// ---- result records in another GPU's memory (multi-GPU gather without a collective) ----------------------
+int fmpnp_shared_buffer_create(fmpnp_ctx* ctx, size_t bytes, void** dev_ptr, unsigned char* handle) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!dev_ptr || !handle || bytes == 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad shared_buffer_create arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == FMPNP_IPC_HANDLE_BYTES, "IPC handle size");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    void* p = nullptr;
+    FMPNP_CUDA(ctx, cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaMemset(p, 0, bytes);
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return fail(ctx, FMPNP_ERR_CUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+    }
+    memcpy(handle, &h, sizeof(h));
+    *dev_ptr = p;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_shared_buffer_open(fmpnp_ctx* ctx, const unsigned char* handle, void** dev_ptr) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!dev_ptr || !handle) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad shared_buffer_open arguments");
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    FMPNP_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *dev_ptr = p;
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_shared_buffer_close(fmpnp_ctx* ctx, void* dev_ptr) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!dev_ptr) return FMPNP_SUCCESS;
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, cudaIpcCloseMemHandle(dev_ptr));
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_shared_buffer_destroy(fmpnp_ctx* ctx, void* dev_ptr) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (!dev_ptr) return FMPNP_SUCCESS;
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, cudaFree(dev_ptr));
+    return FMPNP_SUCCESS;
+}
+
+int fmpnp_copy_to_host(fmpnp_ctx* ctx, void* dst_host, const void* src_dev, size_t bytes, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (bytes == 0) return FMPNP_SUCCESS;
+    if (!dst_host || !src_dev) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "bad copy_to_host arguments");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    FMPNP_CUDA(ctx, cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, stream));
+    FMPNP_CUDA(ctx, cudaStreamSynchronize(stream));
     return FMPNP_SUCCESS;
 }
 

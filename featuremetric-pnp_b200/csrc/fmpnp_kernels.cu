@@ -304,7 +304,24 @@ __device__ __forceinline__ void enqueue_evaluation(const SchedDev& s, int q, int
     for (int u = 0; u < units; ++u) {
         const unsigned int pos = base + (unsigned int)u;
         const unsigned long long v = ((unsigned long long)pos << 32) | (unsigned int)(q * kRanges + u + 1);
-        *reinterpret_cast<volatile unsigned long long*>(&s.queue[pos & (s.cap - 1)]) = v;
+        volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(&s.queue[pos & (s.cap - 1)]);
+        // A slot is written only while it is empty: its consumer of the previous lap (ticket pos - cap) hands it back
+        // after reading it.  The FIFO holds twice the tasks that can be queued at once, so this never waits in
+        // practice; it is what makes overwriting an entry that has not been taken yet impossible, not just unlikely.
+        unsigned long long t0 = 0;
+        for (uint32_t spin = 0; *slot != kQueueEmpty; ++spin) {
+            if (ld_volatile_u32(s.error) != 0u) return;
+            if ((spin & 1023u) == 1023u) {
+                const unsigned long long now = global_timer_ns();
+                if (t0 == 0) t0 = now;
+                if (s.wait_limit_ns != 0 && now - t0 > s.wait_limit_ns) {  // give up instead of hanging
+                    atomicExch(s.error, 1u);
+                    return;
+                }
+            }
+            __nanosleep(100);
+        }
+        *slot = v;
     }
 }
 
@@ -317,6 +334,7 @@ __device__ __forceinline__ int dequeue_task(const SchedDev& s, int B) {
         const unsigned long long v = ld_volatile_u64(slot);
         if (v != kQueueEmpty && (unsigned int)(v >> 32) == ticket) {
             __threadfence();
+            *reinterpret_cast<volatile unsigned long long*>(const_cast<unsigned long long*>(slot)) = kQueueEmpty;  // hand the slot back
             return (int)(unsigned int)(v & 0xffffffffu) - 1;
         }
         if (ld_volatile_u32(s.done) >= (unsigned int)B || ld_volatile_u32(s.error) != 0u) return -1;

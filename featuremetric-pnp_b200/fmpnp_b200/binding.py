@@ -106,6 +106,14 @@ def lib():
             L.fmpnp_blur_chw.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                          C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
             L.fmpnp_blur_chw.restype = C.c_int
+            L.fmpnp_shared_buffer_create.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
+            L.fmpnp_shared_buffer_open.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+            L.fmpnp_shared_buffer_close.argtypes = [C.c_void_p, C.c_void_p]
+            L.fmpnp_shared_buffer_destroy.argtypes = [C.c_void_p, C.c_void_p]
+            L.fmpnp_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+            for fn in (L.fmpnp_shared_buffer_create, L.fmpnp_shared_buffer_open, L.fmpnp_shared_buffer_close,
+                       L.fmpnp_shared_buffer_destroy, L.fmpnp_copy_to_host):
+                fn.restype = C.c_int
             _lib = L
     return _lib
 
@@ -190,6 +198,54 @@ def loss_id_of(loss):
         return LOSS_IDS[name], 0.0
     raise FmpnpError("loss_fn %r is not one of %s: arbitrary Python losses cannot run inside the CUDA kernel"
                      % (loss, sorted(LOSS_IDS)))
+
+
+class SharedRecords:
+    """Result records of ALL ranks in the memory of one GPU (fmpnp_shared_buffer_*): the owner creates the buffer and
+    ships `handle` (64 bytes) to the other ranks, who open it; `block(first, count)` is what a rank passes to
+    refine_batch(out=...) so that its kernels store their records straight into the owner's memory over NVLink.
+    No collective, no extra kernel; the records of a launch are complete once the WRITING rank has synchronised
+    its stream (the owner reads after a barrier)."""
+
+    class _Range:
+        def __init__(self, ptr):
+            self._ptr = ptr
+
+        def data_ptr(self):
+            return self._ptr
+
+    def __init__(self, n_records, handle=None, ctx=None):
+        self.ctx = ctx or default_context()
+        self.n_records, self.owner = int(n_records), handle is None
+        p = C.c_void_p()
+        if self.owner:
+            buf = C.create_string_buffer(64)
+            self.ctx.check(lib().fmpnp_shared_buffer_create(self.ctx._h, self.n_records * RESULT_DTYPE.itemsize,
+                                                            C.byref(p), buf), "fmpnp_shared_buffer_create")
+            self.handle = bytes(buf.raw)
+        else:
+            self.handle = bytes(handle)
+            self.ctx.check(lib().fmpnp_shared_buffer_open(self.ctx._h, self.handle, C.byref(p)),
+                           "fmpnp_shared_buffer_open")
+        self.ptr = p.value
+
+    def block(self, first, count):
+        if first < 0 or first + count > self.n_records:
+            raise FmpnpError("record block [%d, %d) outside the %d shared records" % (first, first + count, self.n_records))
+        return SharedRecords._Range(self.ptr + first * RESULT_DTYPE.itemsize)
+
+    def read(self):
+        """All records as a host numpy structured array (any rank that has the buffer mapped may read)."""
+        out = np.empty(self.n_records, dtype=RESULT_DTYPE)
+        self.ctx.check(lib().fmpnp_copy_to_host(self.ctx._h, out.ctypes.data_as(C.c_void_p), C.c_void_p(self.ptr),
+                                                out.nbytes, _stream_ptr()), "fmpnp_copy_to_host")
+        return out
+
+    def close(self):
+        if getattr(self, "ptr", None):
+            fn = lib().fmpnp_shared_buffer_destroy if self.owner else lib().fmpnp_shared_buffer_close
+            fn(self.ctx._h, C.c_void_p(self.ptr))
+            self.ptr = None
 
 
 class Problem:
@@ -335,6 +391,8 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     ctx.check(rc, "fmpnp_refine_batch")
     ret = {"results_dev": res_dev, "results": None}
     if sync:
+        if not isinstance(res_dev, torch.Tensor):
+            raise FmpnpError("sync=True needs a torch tensor as `out` (a raw device range is read by its owner)")
         ret["results"] = res_dev[:B].cpu().numpy().view(RESULT_DTYPE).reshape(B)
         if B and int(ret["results"]["status"].min()) < 0:
             raise FmpnpError("fmpnp_refine_batch: the device scheduler gave up (FMPNP_STATUS_INCOMPLETE)")

@@ -19,12 +19,37 @@ def shard_range(n_queries, rank, world_size):
     return lo, hi
 
 
+_gather_buffers = {}
+
+
+def shared_result_records(n_queries, group=None, ctx=None, owner_rank=0):
+    """The multi-GPU result gather without a collective: rank `owner_rank` allocates one buffer for the records of
+    ALL queries (fmpnp_shared_buffer_create) and broadcasts its 64-byte handle; every other rank maps it.  A rank then
+    passes `records.block(lo, hi - lo)` (its shard_range) to refine_batch(out=...): the kernel's own stores of the
+    176-byte records travel over NVLink peer access.  The owner reads them (`records.read()`) after every rank has
+    synchronised its stream and a barrier.  NCCL / CUDA only (gloo ranks use gather_result_records)."""
+    from .binding import SharedRecords
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return SharedRecords(n_queries, ctx=ctx)
+    box = [None]
+    rec = None
+    if rank == owner_rank:
+        rec = SharedRecords(n_queries, ctx=ctx)
+        box[0] = rec.handle
+    dist.broadcast_object_list(box, src=owner_rank, group=group)
+    if rank != owner_rank:
+        rec = SharedRecords(n_queries, handle=box[0], ctx=ctx)
+    return rec
+
+
 def gather_result_records(local_records, n_queries, group=None, async_op=False):
     """All-gathers per-rank result records.
 
     local_records: uint8 tensor [n_local, record_bytes] (device tensor under NCCL, CPU under gloo)
     holding this rank's block as laid out by shard_range.  Returns [n_queries, record_bytes] on
-    every rank, in global query order.  With `async_op=True` returns (records, work): the collective runs
+    every rank, in global query order (a view of a buffer that the next call with the same shapes overwrites).
+    With `async_op=True` returns (records, work): the collective runs
     on the backend's own stream, so the caller's next kernels do not wait for the other ranks; call
     `work.wait()` (if not None) before reading `records`."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
@@ -36,9 +61,13 @@ def gather_result_records(local_records, n_queries, group=None, async_op=False):
     lo, hi = shard_range(n_queries, rank, world)
     if local_records.shape[0] != hi - lo:
         raise ValueError("rank %d holds %d records, expected %d" % (rank, local_records.shape[0], hi - lo))
-    pad = torch.zeros((per, rec), dtype=torch.uint8, device=local_records.device)
+    key = (str(local_records.device), world, per, rec)  # send / receive buffers are allocated once per shape
+    if key not in _gather_buffers:
+        _gather_buffers.clear()
+        _gather_buffers[key] = (torch.zeros((per, rec), dtype=torch.uint8, device=local_records.device),
+                                torch.empty((world * per, rec), dtype=torch.uint8, device=local_records.device))
+    pad, out = _gather_buffers[key]
     pad[: hi - lo] = local_records
-    out = torch.empty((world * per, rec), dtype=torch.uint8, device=local_records.device)
     work = dist.all_gather_into_tensor(out, pad, group=group, async_op=async_op)
     return (out[:n_queries], work) if async_op else out[:n_queries]
 

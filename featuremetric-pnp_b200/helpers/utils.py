@@ -68,11 +68,29 @@ def geman_mcclure_loss(x):
     return barron_loss(x, -2.0)
 
 
-def sobel_filter(feature_map, batch=False, normalized=False):
+@gin.configurable
+def sobel_normalization(normalized=False):
+    """Whether the 3x3 Sobel kernels are scaled by 1/8.  PARITY UNPINNED: the reference calls
+    kornia.filters.spatial_gradient with its defaults (utils.py:97,101) and pins kornia 0.2.2, which is neither
+    vendored nor installable offline; newer kornia releases default to the normalised kernel, while the only
+    in-repo evidence -- the toy notebook's stored cost trace and the vendored helpers/sobel_pytorch.py -- needs the
+    un-normalised one.  So the choice is explicit and gin-bindable instead of silent:
+
+        sobel_normalization.normalized = True      # in the .gin file, if the deployment's kornia normalises
+
+    Every place that builds gradient maps (sobel_filter below, build_problem of the device-side adapter, the
+    resampled pyramid levels of model.multilevel_optimization) asks this function."""
+    return bool(normalized)
+
+
+def sobel_filter(feature_map, batch=False, normalized=None):
     """3x3 Sobel d/dx, d/dy of a (C, H, W) map [(B, C, H, W) with batch=True]; returns
     (grad_x, grad_y) shaped like the input (reference utils.py:81-104, which delegates to
-    kornia.filters.spatial_gradient).  Un-normalised kernel with replicate padding: the variant
-    that reproduces the reference notebook's stored known answer."""
+    kornia.filters.spatial_gradient).  Replicate padding; `normalized=None` takes sobel_normalization()
+    (default: the un-normalised kernel, which reproduces the reference notebook's stored known answer,
+    SURVEY.md section 4)."""
+    if normalized is None:
+        normalized = sobel_normalization()
     assert feature_map.dim() > 2
     x = feature_map if batch else feature_map[None]
     b, c, h, w = x.shape

@@ -32,7 +32,7 @@ except ImportError:  # pragma: no cover
 
 import fmpnp_b200 as _fm
 from helpers.utils import (barron_loss, cauchy_loss, gaussian_kernel2d, geman_mcclure_loss, huber_loss,  # noqa: F401
-                           scaled_loss, sobel_filter, squared_loss)
+                           scaled_loss, sobel_filter, sobel_normalization, squared_loss)
 
 # ------------------------------------------------------------------------------------------------
 # packing cache: CHW (reference layout) -> HWC fp32 on the device, keyed by the source tensor
@@ -253,7 +253,7 @@ class sparseFeaturePnP(nn.Module):
                     local = _fm.resize_bilinear_chw(local, int(target_size), int(target_size))
                 if kernel_size is not None:
                     local = _fm.blur_chw(local, gaussian_kernel2d(int(kernel_size), 1.0), pad=1)
-                F, Gx, Gy = _fm.sobel_pack(local)
+                F, Gx, Gy = _fm.sobel_pack(local, normalized=sobel_normalization())
             prob = _fm.Problem(F, Gx, Gy, ref_l, pts, torch.as_tensor(K).double().cpu(), torch.as_tensor(R).double().cpu(),
                                torch.as_tensor(t).double().cpu(), int(im_width), int(im_height))
             R, t = self.forward_packed(prob, track=track)

@@ -19,6 +19,7 @@ except ImportError:  # pragma: no cover
     from helpers import _gin_shim as gin
 
 import fmpnp_b200 as _fm
+from helpers.utils import sobel_filter, sobel_normalization
 from model import _device, find_inliers, sparseFeaturePnP  # noqa: F401
 from pose_prediction import matrix_utils
 
@@ -45,12 +46,17 @@ def _reference_cells(reference_hypercolumns, reference_inliers, image_shape):
     return ref2d[:, 0].contiguous(), ref2d[:, 1].contiguous()
 
 
-def build_problem(query_hypercolumns, reference_hypercolumns, prediction, K, image_shape):
+def build_problem(query_hypercolumns, reference_hypercolumns, prediction, K, image_shape, sobel_normalized=None):
     """Device-resident optimizer inputs of one query (an fmpnp_b200.Problem) from the two hypercolumns
-    and a solve_pnp `Prediction` (fields used: points_3d, reference_inliers, matrix)."""
+    and a solve_pnp `Prediction` (fields used: points_3d, reference_inliers, matrix).
+    `sobel_normalized`: 1/8-scaled Sobel kernels or not; None = helpers.utils.sobel_normalization() (gin-bindable;
+    the reference's kornia default is unpinned, see there)."""
     q = _chw_on_device(query_hypercolumns)
     r = _chw_on_device(reference_hypercolumns)
-    F, Gx, Gy = _fm.sobel_pack(q)  # sobel_filter(feature_map_query) fused with the HWC pack (:57, :61)
+    if sobel_normalized is None:
+        sobel_normalized = sobel_normalization()
+    # sobel_filter(feature_map_query) fused with the HWC pack (:57, :61)
+    F, Gx, Gy = _fm.sobel_pack(q, normalized=bool(sobel_normalized))
     rows, cols = _reference_cells(r, prediction.reference_inliers, image_shape)
     ref = _fm.gather_descriptors(r, rows, cols)  # feature_ref (:56)
     pts = torch.from_numpy(np.ascontiguousarray(prediction.points_3d, dtype=np.float64).reshape(-1, 3)).to(q.device)
@@ -73,9 +79,16 @@ def feature_pnp(query_hypercolumns, reference_hypercolumns, prediction, K, image
         R, t = model.forward_packed(prob, track=track)
     else:
         if any(ts is not None or ks is not None for _, _, ts, ks in feature_pyramid):
-            raise NotImplementedError("resized / blurred pyramid levels need the CHW map: call "
-                                      "model.multilevel_optimization with the reference's tensors")
-        R, t = model.multilevel_packed([(s, e) for s, e, _, _ in feature_pyramid], prob, track=track)
+            # resized / blurred levels (model.py:196-207) are rebuilt from the CHW hypercolumn level by level: the
+            # drop-in multilevel_optimization does that on the device (resize / blur / Sobel + pack kernels)
+            q = _chw_on_device(query_hypercolumns)
+            gx, gy = sobel_filter(q)
+            R, t = model.multilevel_optimization(
+                feature_pyramid, prob.pts3D, prob.ref, q, gx, gy, torch.from_numpy(prob.K.reshape(3, 3).copy()),
+                prob.im_width, prob.im_height, R_init=torch.from_numpy(prob.R0.reshape(3, 3).copy()),
+                t_init=torch.from_numpy(prob.t0.copy()), track=track)
+        else:
+            R, t = model.multilevel_packed([(s, e) for s, e, _, _ in feature_pyramid], prob, track=track)
     return R, t, model
 
 

@@ -19,7 +19,10 @@
  *     host pointer is the device pointer): the kernels then fetch only the rows they gather over
  *     PCIe ("zero-copy") and the caller does not upload whole maps;
  *   - launches are asynchronous on the `stream` argument (a `cudaStream_t` passed as void*);
- *     a context must not be used from two host threads at once;
+ *     a context must not be used from two host threads at once.  A context owns ONE
+ *     workspace: a call issued on a different stream than the previous call is ordered behind it on the device
+ *     (cudaStreamWaitEvent), so launches of one context never overlap -- use one context per stream for
+ *     concurrency;
  *   - there is NO CPU fallback: without a CUDA device fmpnp_create() fails.
  *
  * Data layout (differs from the reference on purpose): dense maps are
@@ -37,7 +40,7 @@
 extern "C" {
 #endif
 
-#define FMPNP_VERSION 101
+#define FMPNP_VERSION 102
 #define FMPNP_MAX_LEVELS 8
 
 typedef struct fmpnp_ctx fmpnp_ctx;
@@ -232,6 +235,23 @@ int64_t fmpnp_launch_count(const fmpnp_ctx *ctx);
  * tasks per pose evaluation (0 = one CTA / cluster per query, no task queue).  Diagnostics. */
 int fmpnp_last_geometry(const fmpnp_ctx *ctx, int32_t *grid, int32_t *cluster_size, int32_t *ring_bytes,
                         int32_t *tasks_per_evaluation);
+
+/* Result records written straight into another GPU's memory (queries are sharded over the
+ * GPUs of one box, the only exchange is the final gather of the fixed-size result records; the reference shards
+ * a slice over independent jobs the same way, submit_cmu_auto.sh:17-43).  The gathering rank creates one buffer
+ * for all queries and passes the 64-byte handle to the other ranks (any transport); they open it and hand
+ * `opened + first_query * sizeof(fmpnp_result)` to fmpnp_refine_batch as `results`: the kernel's own stores of
+ * the records travel over NVLink / PCIe peer access, no collective and no extra kernel.  The records of a launch
+ * are complete once its stream has been synchronised on the WRITING rank.
+ *   create : cudaMalloc + zero + cudaIpcGetMemHandle on the context's device
+ *   open   : cudaIpcOpenMemHandle (peer access enabled lazily); close with fmpnp_shared_buffer_close
+ *   fmpnp_copy_to_host : synchronous D2H of any device range (reading the gathered records without torch) */
+#define FMPNP_IPC_HANDLE_BYTES 64
+int fmpnp_shared_buffer_create(fmpnp_ctx *ctx, size_t bytes, void **dev_ptr, unsigned char *handle);
+int fmpnp_shared_buffer_open(fmpnp_ctx *ctx, const unsigned char *handle, void **dev_ptr);
+int fmpnp_shared_buffer_close(fmpnp_ctx *ctx, void *dev_ptr);
+int fmpnp_shared_buffer_destroy(fmpnp_ctx *ctx, void *dev_ptr);
+int fmpnp_copy_to_host(fmpnp_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes, void *stream);
 
 /* sizeof() of the ABI structs (0 problem, 1 options, 2 result, 3 history), so that a binding
  * in another language can verify its mirrors; -1 for an unknown index. */

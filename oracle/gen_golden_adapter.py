@@ -154,8 +154,21 @@ def save(name, case, cfg, out):
                                                             os.path.getsize(path) // 1024))
 
 
-def run_feature_pnp(name, case, n_iters, loss, lambda_, ratio, pyramid=None):
+def run_feature_pnp(name, case, n_iters, loss, lambda_, ratio, pyramid=None, sobel_normalized=False):
+    """`sobel_normalized`: run the reference with a kornia whose spatial_gradient scales the Sobel kernels by 1/8
+    (what newer kornia releases do by default; the reference's pinned 0.2.2 cannot be checked offline)."""
     mod, ref_model, ref_utils = load_reference_adapter()
+    if sobel_normalized:
+        plain = ref_utils.kornia.filters.spatial_gradient
+        ref_utils.kornia.filters.spatial_gradient = functools.partial(plain, normalized=True)
+    try:
+        _run_feature_pnp(mod, ref_model, ref_utils, name, case, n_iters, loss, lambda_, ratio, pyramid, sobel_normalized)
+    finally:
+        if sobel_normalized:
+            ref_utils.kornia.filters.spatial_gradient = plain
+
+
+def _run_feature_pnp(mod, ref_model, ref_utils, name, case, n_iters, loss, lambda_, ratio, pyramid, sobel_normalized):
     mod.sparseFeaturePnP = functools.partial(ref_model.sparseFeaturePnP, n_iters=n_iters, loss_fn=getattr(ref_utils, loss),
                                              lambda_=lambda_, ratio_threshold=ratio)
     K = torch.from_numpy(case["K"])
@@ -167,7 +180,10 @@ def run_feature_pnp(name, case, n_iters, loss, lambda_, ratio, pyramid=None):
     out.update(out_R=R.numpy().copy(), out_t=t.numpy().copy(), quaternion=mod.matrix_utils.matrix_quaternion(T))
     cfg = dict(kind="feature_pnp", n_iters=np.int32(n_iters), loss=loss, lambda_=np.float64(lambda_),
                ratio_threshold=np.float64(np.nan if ratio is None else ratio),
-               levels=np.array([[s, e] for s, e, _, _ in pyramid] if pyramid else np.zeros((0, 2)), dtype=np.int32))
+               levels=np.array([[s, e] for s, e, _, _ in pyramid] if pyramid else np.zeros((0, 2)), dtype=np.int32),
+               pyramid4=np.array([[s, e, -1 if ts is None else ts, -1 if ks is None else ks] for s, e, ts, ks in pyramid]
+                                 if pyramid else np.zeros((0, 4)), dtype=np.int32),
+               sobel_normalized=np.int32(1 if sobel_normalized else 0))
     save(name, case, cfg, out)
 
 
@@ -216,6 +232,9 @@ def main():
     run_feature_pnp("adapter_pnp_pyramid", make_adapter_case(2), 8, "squared_loss", 0.01, 0.8,
                     pyramid=[(16, 32, None, None), (4, 16, None, None), (0, 4, None, None)])
     run_feature_pnp("adapter_pnp_float", make_adapter_case(3, quantised=False), 12, "cauchy_loss", 0.01, None)
+    run_feature_pnp("adapter_pnp_norm", make_adapter_case(6), 12, "geman_mcclure_loss", 0.01, None, sobel_normalized=True)
+    run_feature_pnp("adapter_pnp_resampled", make_adapter_case(7, C=24), 8, "squared_loss", 0.01, None,
+                    pyramid=[(16, 24, 16, None), (8, 16, None, 3), (0, 8, None, None)])
     run_feature_pnp_multi("adapter_multi_mask", make_adapter_case(4), 6, "squared_loss", 0.01, 0.8)
     run_feature_pnp_multi("adapter_multi_nomask", make_adapter_case(5, with_mask=False), 6, "squared_loss", 0.01, 0.8)
     run_resampled_pyramid("pyramid_resampled_a", 21, [(16, 24, 16, None), (8, 16, None, 3), (0, 8, None, None)])

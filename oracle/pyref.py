@@ -31,8 +31,25 @@ def load():
             sys.modules.pop(k, None)
         sys.path.insert(0, os.path.join(REFERENCE_ROOT, "featurePnP"))
         sys.path.insert(0, _SHIM)
+        # The reference's `helpers` directory has no __init__.py (a namespace package): any regular package called
+        # `helpers` further down sys.path -- the product's drop-in one -- would win the import, and the reference's
+        # model.py would silently run on the product's re-implementation of utils.py.  Load the reference's file by
+        # path and register it under the names model.py imports.
+        import importlib.util
+        import types
+        hdir = os.path.join(REFERENCE_ROOT, "featurePnP", "helpers")
+        pkg = types.ModuleType("helpers")
+        pkg.__path__ = [hdir]
+        sys.modules["helpers"] = pkg
+        spec = importlib.util.spec_from_file_location("helpers.utils", os.path.join(hdir, "utils.py"))
+        ref_utils = importlib.util.module_from_spec(spec)
+        sys.modules["helpers.utils"] = ref_utils
+        spec.loader.exec_module(ref_utils)
+        pkg.utils = ref_utils
         ref_model = importlib.import_module("model")
-        ref_utils = importlib.import_module("helpers.utils")
+        assert os.path.realpath(ref_model.__file__).startswith(os.path.realpath(REFERENCE_ROOT)), ref_model.__file__
+        assert os.path.realpath(ref_utils.__file__).startswith(os.path.realpath(REFERENCE_ROOT)), ref_utils.__file__
+        assert sys.modules["helpers.utils"] is ref_utils and ref_model.squared_loss is ref_utils.squared_loss
     finally:
         sys.path[:] = saved_path
         for k, v in saved_mods.items():

@@ -156,6 +156,50 @@ def test_feature_pnp_matches_reference_adapter(name, tol, device, monkeypatch):
     assert np.abs(matrix_utils.matrix_quaternion(T) - g["quaternion"]).max() < 1e-7
 
 
+def test_feature_pnp_with_normalised_sobel_matches_reference_adapter(monkeypatch):
+    """The Sobel normalisation of the reference's kornia is unpinned (helpers.utils.sobel_normalization): the fixture
+    was produced by the reference adapter on a kornia stand-in that scales the kernels by 1/8; the adapter follows
+    when `sobel_normalization.normalized = True` is bound, and does NOT match with the un-normalised default."""
+    import helpers.utils as hu
+    import model
+    from pose_prediction import optimize_feature_pnp as adapter
+    g = load("adapter_pnp_norm")
+    assert int(g["sobel_normalized"]) == 1
+    monkeypatch.setattr(adapter, "sparseFeaturePnP", functools.partial(
+        model.sparseFeaturePnP, n_iters=int(g["n_iters"]), loss_fn=getattr(hu, g["loss"]), lambda_=float(g["lambda_"])))
+    args = (torch.from_numpy(g["qh"]).cuda(), torch.from_numpy(g["rh"]).cuda(), prediction_of(g), torch.from_numpy(g["K"]),
+            [int(v) for v in g["image_shape"]])
+    monkeypatch.setattr(adapter, "sobel_normalization", lambda: True)
+    R, t, m = adapter.feature_pnp(*args, track=True)
+    check_track("adapter_pnp_norm", m, g, TIGHT)
+    assert np.abs(R.numpy() - g["out_R"]).max() < 1e-7 and np.abs(t.numpy() - g["out_t"]).max() < 1e-7
+    monkeypatch.setattr(adapter, "sobel_normalization", lambda: False)
+    R2, t2, m2 = adapter.feature_pnp(*args, track=True)
+    assert np.abs(t2.numpy() - g["out_t"]).max() > 1e-6  # an 8x gradient scale is not a detail
+    prob = adapter.build_problem(*args, sobel_normalized=True)
+    prob_raw = adapter.build_problem(*args)
+    assert torch.equal(prob.Gx * 8.0, prob_raw.Gx) and torch.equal(prob.F, prob_raw.F)
+
+
+def test_feature_pnp_with_resampled_levels_matches_reference_adapter(monkeypatch):
+    """feature_pnp with target_size / kernel_size pyramid levels (optimize_feature_pnp.py:63-69 -> model.py:193-210):
+    rebuilt per level on the device from the CHW hypercolumn.  (The Gaussian window is kornia's: parity unpinned.)"""
+    import helpers.utils as hu
+    import model
+    from pose_prediction import optimize_feature_pnp as adapter
+    model.clear_pack_cache()
+    g = load("adapter_pnp_resampled")
+    pyr = [(int(s), int(e), None if ts < 0 else int(ts), None if ks < 0 else int(ks)) for s, e, ts, ks in g["pyramid4"]]
+    assert any(ts is not None or ks is not None for _, _, ts, ks in pyr)
+    monkeypatch.setattr(adapter, "sparseFeaturePnP", functools.partial(
+        model.sparseFeaturePnP, n_iters=int(g["n_iters"]), loss_fn=getattr(hu, g["loss"]), lambda_=float(g["lambda_"])))
+    R, t, m = adapter.feature_pnp(torch.from_numpy(g["qh"]).cuda(), torch.from_numpy(g["rh"]).cuda(), prediction_of(g),
+                                  torch.from_numpy(g["K"]), [int(v) for v in g["image_shape"]], track=True,
+                                  feature_pyramid=pyr)
+    check_track("adapter_pnp_resampled", m, g, COST_RTOL)
+    assert rot_angle_deg(R.numpy(), g["out_R"]) <= ROT_TOL_DEG and np.abs(t.numpy() - g["out_t"]).max() <= TRANS_TOL_M
+
+
 @pytest.mark.parametrize("name", ["adapter_multi_mask", "adapter_multi_nomask"])
 def test_feature_pnp_multi_matches_reference_adapter(name, monkeypatch):
     import helpers.utils as hu

@@ -65,3 +65,21 @@ def test_find_inliers_and_compute_cost():
     c2 = oracle.compute_cost(g["pts3D"], ref, F, g["K"], g["im_width"], g["im_height"], g["R0"], g["t0"],
                              ratio_threshold=0.7)
     assert abs(c2 - float(g["compute_cost_ratio07"])) <= ORACLE_COST_RTOL * abs(float(g["compute_cost_ratio07"]))
+
+
+def test_fixture_generator_imports_the_reference_own_helpers():
+    """Where the reference is present (the build container), oracle/pyref.py must hand gen_golden*.py the reference's
+    model.py AND the reference's helpers/utils.py -- not the product's drop-in `helpers` package, which is a regular
+    package and would otherwise shadow the reference's namespace package on sys.path."""
+    import os
+    import sys
+    import pyref
+    if not pyref.available():
+        pytest.skip("reference not present (GPU box)")
+    import helpers.utils as product_utils  # the product's package is importable first, as in the generators
+    ref_model, ref_utils = pyref.load()
+    root = os.path.realpath(pyref.REFERENCE_ROOT)
+    assert os.path.realpath(ref_model.__file__).startswith(root) and os.path.realpath(ref_utils.__file__).startswith(root)
+    assert ref_utils is not product_utils and hasattr(ref_utils, "kornia")
+    assert ref_model.squared_loss is ref_utils.squared_loss and ref_model.so3exp_map is ref_utils.so3exp_map
+    assert sys.modules.get("helpers.utils") is product_utils  # and the product's modules are back in place
