@@ -71,7 +71,12 @@ def test_full_size_trajectory_matches_oracle(name, workload):
     plain = fm().refine_batch(probs, N_ITERS, **kw)
     assert same_records(plain["results"], out["results"])
     every = fm().refine_batch(probs, N_ITERS, track=True, gather_every_row=True, **kw)
-    assert_reuse_is_invisible(out, every, len(probs))
+    if cfg["inlier"] is None:
+        assert_reuse_is_invisible(out, every, len(probs))
+    else:  # (the fused selection pass streams four rows when its records are reused and two otherwise: counters differ)
+        assert same_records(out["results"], every["results"], skip=("gathered_rows", "reused_rows"))
+        for k in ("len", "Rs", "ts", "costs", "points2d", "mask", "kept"):
+            assert np.array_equal(out["history"][k], every["history"][k], equal_nan=k in ("Rs", "ts", "costs")), k
     g, r = out["results"]["gathered_rows"].astype(np.float64), out["results"]["reused_rows"].astype(np.float64)
     if workload == "bench":
         assert (r / (g + r)).min() > 0.5, "the bench workload is expected to reuse most records"
