@@ -63,6 +63,8 @@ struct fmpnp_ctx {
 
 namespace {
 
+constexpr int kNoallocRingBytes = 96 * 1024;  // staging ring of fmpnp_compute_cost_batch_noalloc's CTAs (a multiple of 8 x 128)
+
 int fail(fmpnp_ctx* ctx, int code, const char* fmt, ...) {
     if (ctx) {
         va_list ap;
@@ -381,6 +383,10 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     if (ctx->watchdog_s < 0) ctx->watchdog_s = 0;
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     ctx->reuse = env_int("FMPNP_REUSE", 1);
+    {  // fmpnp_compute_cost_batch_noalloc: resolve its scratch array now, so that the call itself only launches
+        void* scratch = nullptr;
+        if (static_scratch_setup(device, kNoallocRingBytes, &scratch) != cudaSuccess) cudaGetLastError();  // reported by the call
+    }
     *out = ctx;
     return FMPNP_SUCCESS;
 }
@@ -537,6 +543,66 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     if (int rc1 = mark_launched(ctx, stream)) return rc1;
     ctx->launches += 1;
     ctx->last = {g.grid, g.cluster, g.ring_bytes, g.units};
+    return FMPNP_SUCCESS;
+}
+
+// No counterpart in the reference: compute_cost for callers that cannot allocate (see include/fmpnp.h).  Calls no
+// cudaMalloc / cudaFree / cudaMallocHost and touches none of the context's workspace: the descriptors are a kernel
+// parameter, the scratch is the library's file-scope device array (fmpnp_kernels.cu).
+int fmpnp_compute_cost_batch_noalloc(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, const fmpnp_options* o,
+                                     double* costs, int32_t* n_supported, void* stream_) {
+    if (!ctx) return FMPNP_ERR_INVALID_ARGUMENT;
+    if (B == 0) return FMPNP_SUCCESS;
+    if (!probs || !o || !costs || B < 0) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "null argument or B < 0");
+    if (B > FMPNP_NOALLOC_MAX_QUERIES)
+        return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT,
+                    "fmpnp_compute_cost_batch_noalloc: %d queries exceed the static scratch (at most %d per call; use "
+                    "fmpnp_compute_cost_batch)", B, FMPNP_NOALLOC_MAX_QUERIES);
+    StaticQueries pack;
+    memset(&pack, 0, sizeof(pack));
+    for (int32_t b = 0; b < B; ++b) {
+        const fmpnp_problem& p = probs[b];
+        int rc = validate_problem(ctx, p, b, false);
+        if (rc) return rc;
+        if (p.N > FMPNP_NOALLOC_MAX_POINTS)
+            return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT,
+                        "fmpnp_compute_cost_batch_noalloc: problem %d has %d points, the static scratch holds at most %d "
+                        "per query (use fmpnp_compute_cost_batch)", b, p.N, FMPNP_NOALLOC_MAX_POINTS);
+        QueryDev& q = pack.q[b];
+        q.F = p.F;
+        q.Gx = p.Gx;
+        q.Gy = p.Gy;
+        q.ref = p.ref;
+        q.pts = p.pts3D;
+        q.active = p.active;
+        memcpy(q.K, p.K, sizeof(q.K));
+        memcpy(q.R0, p.R0, sizeof(q.R0));
+        memcpy(q.t0, p.t0, sizeof(q.t0));
+        q.N = p.N;
+        q.C = p.C;
+        q.Hf = p.Hf;
+        q.Wf = p.Wf;
+        q.im_w = p.im_width;
+        q.im_h = p.im_height;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
+    void* scratch = nullptr;
+    FMPNP_CUDA(ctx, static_scratch_setup(ctx->device, kNoallocRingBytes, &scratch));
+    LaunchParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.B = B;
+    lp.mode = kModeComputeCost;
+    lp.ring_per_warp = kNoallocRingBytes / kWarps;
+    lp.min_depth = 2;
+    lp.cluster_size = 1;  // one CTA per query, no task queue: nothing but records, flags and the counter to keep
+    lp.scheduler = 0;
+    lp.use_ratio = std::isnan(o->ratio_threshold) ? 0 : 1;
+    lp.ratio_thr = lp.use_ratio ? o->ratio_threshold : 0.0;
+    lp.cost_out = costs;
+    lp.nsup_out = n_supported;
+    FMPNP_CUDA(ctx, launch_compute_cost_static(lp, pack, scratch, B, kNoallocRingBytes, stream));
+    ctx->launches += 1;
     return FMPNP_SUCCESS;
 }
 

@@ -32,6 +32,7 @@
 // of 4) take a generic path with direct coalesced global loads instead of the staged one.
 #include <cmath>
 #include <cstdint>
+#include <mutex>
 
 #include <cooperative_groups.h>
 
@@ -906,6 +907,66 @@ int max_active_clusters(int cluster_size, int ring_bytes) {
         return 0;
     }
     return n;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// compute_cost without any allocation (fmpnp_compute_cost_batch_noalloc; no counterpart in the reference).
+// The per-CTA scratch of compute_cost_kernel -- records, support flags, the query counter -- lives in a
+// file-scope device array of a fixed, modest size instead of the context's cudaMalloc'ed workspace, and the
+// problem descriptors travel as a kernel parameter instead of through the context's staging buffers.  Every GPU
+// that loads the library holds the array until the process exits; every call on a device shares it (calls that
+// overlap on the GPU race), and it keeps the last call's contents: the only part that has to start at zero is
+// the query counter, which the launcher clears on the caller's stream (flags are written before they are read,
+// records are read only where the flag says so).
+// ---------------------------------------------------------------------------------------------
+struct StaticScratch {
+    double rec[kStaticMaxQueries][kStaticMaxPoints][kRecDoubles];  // 2 MB
+    uint8_t supp[kStaticMaxQueries][kStaticMaxPoints];             // 32 KB
+    unsigned int counter;
+};
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+__global__ void __launch_bounds__(kThreads, 2)
+    compute_cost_static_kernel(const LaunchParams p, const __grid_constant__ StaticQueries pack) {
+    LaunchParams lp = p;
+    lp.queries = pack.q;  // the descriptors are read from the parameter space: nothing was staged in global memory
+    persistent_body<kModeComputeCost>(lp);
+}
+
+// Set-up, once per device (with that device current): the device address of the scratch array -- in host code
+// its name is only a stand-in -- and the dynamic shared memory the kernel may ask for.  Allocates nothing.
+cudaError_t static_scratch_setup(int device, int ring_bytes, void** scratch) {
+    constexpr int kMaxDevices = 64;
+    static void* ptrs[kMaxDevices] = {nullptr};
+    static std::mutex mu;
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[device] == nullptr) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(compute_cost_static_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ring_bytes);
+        if (e != cudaSuccess) return e;
+        ptrs[device] = ptr;
+    }
+    *scratch = ptrs[device];
+    return cudaSuccess;
+}
+
+// p.rec / p.supp / p.work_counter are filled in here from `scratch` (the pointer static_scratch_setup returned)
+cudaError_t launch_compute_cost_static(LaunchParams p, const StaticQueries& pack, void* scratch, int grid, int ring_bytes,
+                                       cudaStream_t stream) {
+    StaticScratch* s = static_cast<StaticScratch*>(scratch);
+    p.rec = &s->rec[0][0][0];
+    p.supp = &s->supp[0][0];
+    p.inl = nullptr;
+    p.n_max = kStaticMaxPoints;
+    p.work_counter = &s->counter;
+    cudaError_t e = cudaMemsetAsync(&s->counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    compute_cost_static_kernel<<<grid, kThreads, (size_t)ring_bytes, stream>>>(p, pack);
+    return cudaGetLastError();
 }
 
 }  // namespace fmpnp

@@ -137,6 +137,15 @@ cudaError_t launch_bilinear_resize_chw(const void* src, int src_is_f64, double* 
 cudaError_t launch_blur_chw(const void* src, int src_is_f64, const double* kern, double* dst, int Cs, int H, int W, int k,
                             int pad, cudaStream_t stream);
 size_t refine_static_smem_bytes();
+// compute_cost with its scratch in a file-scope device array (fmpnp_compute_cost_batch_noalloc)
+constexpr int kStaticMaxQueries = FMPNP_NOALLOC_MAX_QUERIES;
+constexpr int kStaticMaxPoints = FMPNP_NOALLOC_MAX_POINTS;
+struct StaticQueries {
+    QueryDev q[kStaticMaxQueries];
+};
+cudaError_t static_scratch_setup(int device, int ring_bytes, void** scratch);
+cudaError_t launch_compute_cost_static(LaunchParams p, const StaticQueries& pack, void* scratch, int grid, int ring_bytes,
+                                       cudaStream_t stream);
 int max_active_clusters(int cluster_size, int ring_bytes);
 cudaError_t refine_allow_nonportable_clusters(int allow);
 cudaError_t refine_set_max_dynamic_smem(int bytes);

@@ -29,6 +29,7 @@ from .binding import (  # noqa: F401
     ProblemBatch,
     SharedRecords,
     compute_cost_batch,
+    compute_cost_batch_noalloc,
     default_context,
     find_inliers_batch,
     lib,
@@ -46,7 +47,7 @@ from . import ops  # noqa: E402,F401  (registers torch.ops.fmpnp.*)
 
 __all__ = [
     "LOSS_IDS", "STATUS_OK", "STATUS_EMPTY_SUPPORT", "STATUS_NAN_STEP", "STATUS_NO_INITIAL_COST", "Context",
-    "FmpnpError", "Problem", "ProblemBatch", "SharedRecords", "compute_cost_batch", "default_context", "find_inliers_batch", "lib", "lib_path",
+    "FmpnpError", "Problem", "ProblemBatch", "SharedRecords", "compute_cost_batch", "compute_cost_batch_noalloc", "default_context", "find_inliers_batch", "lib", "lib_path",
     "loss_id_of", "pack_chw_to_hwc", "refine_batch", "sobel_pack", "gather_descriptors", "resize_bilinear_chw",
     "blur_chw",
 ]

@@ -88,6 +88,8 @@ def lib():
             L.fmpnp_compute_cost_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.POINTER(COptions),
                                                    C.c_void_p, C.c_void_p, C.c_void_p]
             L.fmpnp_compute_cost_batch.restype = C.c_int
+            L.fmpnp_compute_cost_batch_noalloc.argtypes = L.fmpnp_compute_cost_batch.argtypes
+            L.fmpnp_compute_cost_batch_noalloc.restype = C.c_int
             L.fmpnp_find_inliers_batch.argtypes = [C.c_void_p, C.POINTER(CProblem), C.c_int32, C.c_int32, C.c_double,
                                                    C.c_double, C.c_void_p, C.c_int32, C.c_void_p]
             L.fmpnp_find_inliers_batch.restype = C.c_int
@@ -416,6 +418,30 @@ def compute_cost_batch(problems, ratio_threshold=None, ctx=None):
                                         C.c_void_p(nsup.data_ptr()), _stream_ptr())
     ctx.check(rc, "fmpnp_compute_cost_batch")
     return costs[:B], nsup[:B]
+
+
+NOALLOC_MAX_QUERIES, NOALLOC_MAX_POINTS = 8, 4096
+
+
+def compute_cost_batch_noalloc(problems, costs, n_supported=None, ratio_threshold=None, ctx=None):
+    """fmpnp_compute_cost_batch_noalloc: compute_cost_batch into the caller's `costs` (float64 [>= B]) and
+    `n_supported` (int32 [>= B] or None) CUDA tensors, without any device allocation -- the scratch is a static
+    array inside the library (at most NOALLOC_MAX_QUERIES problems of NOALLOC_MAX_POINTS points per call; all calls
+    on a device share it, so calls that overlap on the GPU race)."""
+    ctx = ctx or default_context()
+    B = len(problems)
+    if not (costs.is_cuda and costs.dtype == torch.float64 and costs.is_contiguous() and costs.numel() >= B):
+        raise FmpnpError("costs must be a contiguous CUDA float64 tensor with at least B elements")
+    if n_supported is not None and not (n_supported.is_cuda and n_supported.dtype == torch.int32
+                                        and n_supported.is_contiguous() and n_supported.numel() >= B):
+        raise FmpnpError("n_supported must be a contiguous CUDA int32 tensor with at least B elements")
+    o = _options(1, "squared_loss", 0.0, ratio_threshold, None, "cholesky")
+    rc = lib().fmpnp_compute_cost_batch_noalloc(ctx._h, _problem_array(problems), B, C.byref(o),
+                                                C.c_void_p(costs.data_ptr()),
+                                                C.c_void_p(n_supported.data_ptr()) if n_supported is not None else None,
+                                                _stream_ptr())
+    ctx.check(rc, "fmpnp_compute_cost_batch_noalloc")
+    return costs[:B], (n_supported[:B] if n_supported is not None else None)
 
 
 def find_inliers_batch(problems, threshold, loss="squared_loss", barron_alpha=None, ctx=None, out=None):

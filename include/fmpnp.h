@@ -190,6 +190,22 @@ int fmpnp_refine_batch(fmpnp_ctx *ctx, const fmpnp_problem *probs, int32_t B, co
 int fmpnp_compute_cost_batch(fmpnp_ctx *ctx, const fmpnp_problem *probs, int32_t B, const fmpnp_options *opts,
                              double *costs, int32_t *n_supported, void *stream);
 
+/* No counterpart in the reference.  fmpnp_compute_cost_batch for
+ * callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): same arguments, same results (bit for bit), but the call performs NO cudaMalloc / cudaFree /
+ * cudaMallocHost and uses none of the context's workspace.  The problem descriptors travel as a kernel parameter
+ * and the kernel's scratch (per-point records and flags, the query counter) is a file-scope `static __device__`
+ * array of sizeof = FMPNP_NOALLOC_MAX_QUERIES x FMPNP_NOALLOC_MAX_POINTS x 65 bytes (about 2.1 MB) that every GPU
+ * which loads the library holds until the process exits.  Limits: B <= FMPNP_NOALLOC_MAX_QUERIES problems per call
+ * and N <= FMPNP_NOALLOC_MAX_POINTS points per problem; anything larger is rejected with
+ * FMPNP_ERR_INVALID_ARGUMENT (and a message naming the limit), never truncated.  ALL calls on a device share the
+ * one array, whatever their context or stream: two calls that overlap on the GPU race, so order them on one stream
+ * (or with events).  The array keeps the last call's contents; the library clears what has to start at zero. */
+#define FMPNP_NOALLOC_MAX_QUERIES 8
+#define FMPNP_NOALLOC_MAX_POINTS 4096
+int fmpnp_compute_cost_batch_noalloc(fmpnp_ctx *ctx, const fmpnp_problem *probs, int32_t B, const fmpnp_options *opts,
+                                     double *costs, int32_t *n_supported, void *stream);
+
 /* Replaces find_inliers (model.py:131-152), mode "ratio_max", at pose (R0, t0):
  * inliers[b][n] = supported(n) && |rho_n| < threshold * max |rho|.  inliers: DEVICE [B][n_stride]. */
 int fmpnp_find_inliers_batch(fmpnp_ctx *ctx, const fmpnp_problem *probs, int32_t B, int32_t loss_id,
