@@ -54,6 +54,8 @@ struct fmpnp_ctx {
     // record reuse: generations handed out so far (tags of `d_rec` hold generation << 32 | cell, never generation 0)
     uint64_t reuse_next = 1;
     int reuse = 1;  // FMPNP_REUSE=0: gather every row at every evaluation, whatever the options say
+    int l2_policy = 1;  // FMPNP_L2_POLICY=0: no L2 eviction preference for gathered rows / staged records
+    int light = -1;  // FMPNP_LIGHT: 1 / 0 = the light evaluations of a launch with record reuse always / never take their own route (fmpnp_light.cuh); -1 = automatic
     // One workspace per context: a call issued on another stream than the previous one waits for that call's
     // kernels first (cudaStreamWaitEvent), so that two launches of a context never overlap on the device.
     cudaEvent_t last_done = nullptr;
@@ -201,6 +203,10 @@ struct Geometry {
     int grid, ring_bytes, ring_per_warp, min_depth, cluster, units;
 };
 
+// Light evaluations are run as a whole by one CTA: worth it when there are enough queries to keep the CTAs busy that way
+// (otherwise an evaluation is better cut into tasks; same bits either way)
+bool light_route(const fmpnp_ctx* ctx, int32_t B) { return ctx->light >= 0 ? ctx->light != 0 : (int64_t)B * 2 >= ctx->sm_count; }
+
 int32_t max_points(const fmpnp_problem* probs, int32_t B) {
     int32_t n_max = 1;
     for (int32_t b = 0; b < B; ++b)
@@ -209,6 +215,9 @@ int32_t max_points(const fmpnp_problem* probs, int32_t B) {
 }
 
 int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g, bool reuse = false) {
+    // the light evaluations of a launch with record reuse take their own route (LaunchParams::light): the tasks are then
+    // sized for the evaluations that gather
+    if (reuse && light_route(ctx, B)) reuse = false;
     int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
     int S = requested_cluster > 0 ? requested_cluster : ctx->cluster;
     // Task scheduler (default): an evaluation is cut into U tasks so that about three tasks per CTA slot are
@@ -249,7 +258,7 @@ int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Ge
         int ps = per_sm > 0 ? (per_sm > 2 ? 2 : per_sm) : ((work * S <= ctx->sm_count) ? 1 : 2);
         int r = ring > 0 ? ring : (ps == 1 ? budget : 96 * 1024);
         if (r > budget) r = budget;
-        if (r < 72 * 1024) r = 72 * 1024;  // the reductions use a warp's slice as scratch (kWarpScratchDoubles)
+        if (r < kMinRingPerWarp * kWarps) r = kMinRingPerWarp * kWarps;  // the reductions use a warp's slice as scratch
         const int per_warp = (r / kWarps) & ~127;
         if (per_warp < 2 * 128) return fail(ctx, FMPNP_ERR_INVALID_ARGUMENT, "staging ring too small (%d B)", r);
         r = per_warp * kWarps;
@@ -296,6 +305,7 @@ void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, con
     lp.min_depth = g.min_depth;
     lp.cluster_size = g.cluster;
     lp.scheduler = g.units > 0 ? 1 : 0;
+    lp.l2_policy = ctx->l2_policy;
 }
 
 // Task scheduler workspace: per-query LM states, the task FIFO and its counters; reset on the stream.
@@ -383,6 +393,8 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     if (ctx->watchdog_s < 0) ctx->watchdog_s = 0;
     ctx->ctas_per_sm = env_int("FMPNP_CTAS_PER_SM", 0);
     ctx->reuse = env_int("FMPNP_REUSE", 1);
+    ctx->light = env_int("FMPNP_LIGHT", -1);
+    ctx->l2_policy = env_int("FMPNP_L2_POLICY", 1) != 0 ? 1 : 0;
     {  // fmpnp_compute_cost_batch_noalloc: resolve its scratch array now, so that the call itself only launches
         void* scratch = nullptr;
         if (static_scratch_setup(device, kNoallocRingBytes, &scratch) != cudaSuccess) cudaGetLastError();  // reported by the call
@@ -479,6 +491,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     lp.solver = o->solver;
     lp.results = results;
     lp.reuse = (ctx->reuse != 0 && o->gather_every_row == 0) ? 1 : 0;
+    lp.light = lp.reuse && g.cluster == 1 && light_route(ctx, B) ? 1 : 0;
     lp.inlier_on = (o->inlier_threshold == o->inlier_threshold && o->inlier_threshold != 0.0) ? 1 : 0;  // 0 / NaN = off
     lp.inlier_thr = o->inlier_threshold;
     {  // one generation per (query, level) of this launch; generations are never handed out twice

@@ -28,6 +28,14 @@ __device__ __forceinline__ int32_t cast_i32_x86(double r) {
     return (int32_t)r;
 }
 
+// P = R X + t alone (the same multiply / add chain as in project_point)
+__device__ __forceinline__ void transform_point(const double* __restrict__ R, const double* __restrict__ t, double x, double y,
+                                                double z, double& X, double& Y, double& Z) {
+    X = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(R[0], x), __dmul_rn(R[1], y)), __dmul_rn(R[2], z)), t[0]);
+    Y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(R[3], x), __dmul_rn(R[4], y)), __dmul_rn(R[5], z)), t[1]);
+    Z = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(R[6], x), __dmul_rn(R[7], y)), __dmul_rn(R[8], z)), t[2]);
+}
+
 __device__ __forceinline__ Proj project_point(const double* __restrict__ R, const double* __restrict__ t,
                                                const double* __restrict__ K, double x, double y, double z,
                                                int32_t im_w, int32_t im_h) {
@@ -295,6 +303,37 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
 __device__ __forceinline__ void cp_async16_s(uint32_t smem_dst, const void* gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
 }
+// L2 eviction policies (createpolicy): the rows a gather streams are read once -- evict_first keeps them from displacing
+// what IS read again, the per-point records and coordinates (evict_last), which the light evaluations of a launch with
+// record reuse read from L2 twenty times over.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_normal() {
+    uint64_t p;
+    asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+// 16-byte asynchronous copies with an L2 policy
+__device__ __forceinline__ void cp_async16_pol(uint32_t smem_dst, const void* gmem_src, uint64_t pol) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gmem_src), "l"(pol) : "memory");
+}
+template <int OFF>
+__device__ __forceinline__ void cp_async16_pol_off(uint32_t smem_dst, const void* gmem_src, uint64_t pol) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0+%2], [%1+%2], 16, %3;" ::"r"(smem_dst), "l"(gmem_src), "n"(OFF), "l"(pol)
+                 : "memory");
+}
+// 8-byte asynchronous copy (rows of three doubles are only 8-byte aligned); .ca is the only cache operator for this size
+__device__ __forceinline__ void cp_async8_s(uint32_t smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
+}
 // same, both addresses displaced by the compile-time OFF (one address computation serves a whole row)
 template <int OFF>
 __device__ __forceinline__ void cp_async16_off(uint32_t smem_dst, const void* gmem_src) {
@@ -318,6 +357,11 @@ __device__ __forceinline__ void sts64(uint32_t addr, double v) {
 __device__ __forceinline__ double2 lds128d(uint32_t addr) {
     double2 v;
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ double lds64d(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
     return v;
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }

@@ -31,6 +31,7 @@
 // Channel ranges that are not 16-byte aligned (C, slice start or slice length not a multiple
 // of 4) take a generic path with direct coalesced global loads instead of the staged one.
 #include <cmath>
+#include <cstddef>
 #include <cstdint>
 #include <mutex>
 
@@ -39,10 +40,25 @@
 #include "fmpnp_device.cuh"
 #include "fmpnp_kernels.cuh"
 #include "fmpnp_lm.cuh"      // evaluate, solve_and_update, lm_* (includes fmpnp_reduce.cuh, fmpnp_stream.cuh)
+#include "fmpnp_light.cuh"   // light_evaluate
 
 namespace cg = cooperative_groups;
 
 namespace fmpnp {
+
+// evaluate<true>(), or its light form when nearly every record is expected to be in place (fmpnp_light.cuh)
+__device__ __forceinline__ void evaluate_grad(EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp, bool light) {
+    if (light) {
+        light_evaluate(c, R, t, sh, rp);
+        if (threadIdx.x == 0) {
+            sh.n_evals += 1;
+            sh.gathered += (long long)sh.ev_ngath * c.Cl * 4;
+            sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * 4;
+        }
+    } else {
+        evaluate<true>(c, R, t, sh, rp);
+    }
+}
 
 template <int MODE>
 __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
@@ -90,6 +106,8 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
         c.crank = crank;
         c.part_out = nullptr;
         c.limit_given = false;
+        c.row_pol = p.l2_policy ? l2_policy_evict_first() : l2_policy_normal();
+        c.rec_pol = p.l2_policy ? l2_policy_evict_last() : l2_policy_normal();
         c.reuse_gen = 0u;
         c.active = q.active;
         {
@@ -212,7 +230,8 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
 
             // ---- i == 0: cost and linearisation at the incoming pose (model.py:303-359)
             hist_slices(p, qi, sh.hist_len, c);
-            evaluate<true>(c, sh.R, sh.t, sh, rp);
+            const bool can_light = p.light != 0 && csize == 1 && c.reuse_gen != 0u;
+            evaluate_grad(c, sh.R, sh.t, sh, rp, can_light && p.inlier_on && p.n_levels == 0);  // the inlier pass left every record
             __syncthreads();
             if (sh.ev_nsup == 0) {  // model.py:316-320 -> forward returns the CURRENT pose
                 if (tid == 0) {
@@ -236,7 +255,7 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
                 }
                 // ---- trial pose: cost (model.py:428-462) and, if accepted, the next linearisation
                 hist_slices(p, qi, sh.hist_len, c);
-                evaluate<true>(c, sh.Rn, sh.tn, sh, rp);
+                evaluate_grad(c, sh.Rn, sh.tn, sh, rp, can_light);
                 __syncthreads();
                 if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
                     if (tid == 0) {
@@ -351,63 +370,59 @@ __device__ __forceinline__ int dequeue_task(const SchedDev& s, int B) {
     }
 }
 
-// thread 0: query state global <-> shared
-__device__ __forceinline__ void load_state(Shared& sh, const volatile QueryState& g) {  // volatile: L1 may hold a stale copy
-    for (int i = 0; i < 9; ++i) {
-        sh.R[i] = g.R[i];
-        sh.Rn[i] = g.Rn[i];
-        sh.Rb[i] = g.Rb[i];
+// warp 0: query state global <-> shared.  The doubles R .. initial_cost are laid out in the same order in QueryState
+// and in Shared's copy (R, t, Rn, tn, Rb, tb, lin, then the scalars), so the lanes copy them as one array each.
+constexpr int kStatePoseDoubles = 36 + 27;  // R, t, Rn, tn, Rb, tb, lin
+__device__ __forceinline__ void load_state(Shared& sh, const volatile QueryState& g, int lane) {  // volatile: L1 may hold a stale copy
+    static_assert(offsetof(QueryState, lin) == 36 * sizeof(double) && offsetof(Shared, lin) == 36 * sizeof(double), "layout");
+    const volatile double* src = g.R;
+    double* dst = sh.R;
+    for (int i = lane; i < kStatePoseDoubles; i += 32) dst[i] = src[i];
+    if (lane == 0) {
+        sh.prev_cost = g.prev_cost;
+        sh.best_cost = g.best_cost;
+        sh.lambda = g.lambda;
+        sh.lr = g.lr;
+        sh.initial_cost = g.initial_cost;
+        sh.gathered = g.gathered;
+        sh.reused = g.reused;
+    } else if (lane == 1) {
+        sh.best_n = g.best_n;
+        sh.has_best = g.has_best;
+        sh.status = g.status;
+        sh.flag = g.flag;
+        sh.hist_len = g.hist_len;
+        sh.n_evals = g.n_evals;
+        sh.initial_set = g.initial_set;
+    } else if (lane >= 2 && lane < 2 + FMPNP_MAX_LEVELS) {
+        sh.level_status[lane - 2] = g.level_status[lane - 2];
     }
-    for (int i = 0; i < 3; ++i) {
-        sh.t[i] = g.t[i];
-        sh.tn[i] = g.tn[i];
-        sh.tb[i] = g.tb[i];
-    }
-    for (int i = 0; i < 27; ++i) sh.lin[i] = g.lin[i];
-    sh.prev_cost = g.prev_cost;
-    sh.best_cost = g.best_cost;
-    sh.lambda = g.lambda;
-    sh.lr = g.lr;
-    sh.initial_cost = g.initial_cost;
-    sh.gathered = g.gathered;
-    sh.reused = g.reused;
-    sh.best_n = g.best_n;
-    sh.has_best = g.has_best;
-    sh.status = g.status;
-    sh.flag = g.flag;
-    sh.hist_len = g.hist_len;
-    sh.n_evals = g.n_evals;
-    sh.initial_set = g.initial_set;
-    for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) sh.level_status[i] = g.level_status[i];
 }
 
-__device__ __forceinline__ void store_state(const Shared& sh, QueryState& g) {
-    for (int i = 0; i < 9; ++i) {
-        g.R[i] = sh.R[i];
-        g.Rn[i] = sh.Rn[i];
-        g.Rb[i] = sh.Rb[i];
+__device__ __forceinline__ void store_state(const Shared& sh, QueryState& g, int lane) {
+    const double* src = sh.R;
+    double* dst = g.R;
+    for (int i = lane; i < kStatePoseDoubles; i += 32) dst[i] = src[i];
+    if (lane == 0) {
+        g.prev_cost = sh.prev_cost;
+        g.best_cost = sh.best_cost;
+        g.lambda = sh.lambda;
+        g.lr = sh.lr;
+        g.initial_cost = sh.initial_cost;
+        g.gathered = sh.gathered;
+        g.reused = sh.reused;
+    } else if (lane == 1) {
+        g.best_n = sh.best_n;
+        g.has_best = sh.has_best;
+        g.status = sh.status;
+        g.flag = sh.flag;
+        g.hist_len = sh.hist_len;
+        g.n_evals = sh.n_evals;
+        g.initial_set = sh.initial_set;
+    } else if (lane >= 2 && lane < 2 + FMPNP_MAX_LEVELS) {
+        g.level_status[lane - 2] = sh.level_status[lane - 2];
     }
-    for (int i = 0; i < 3; ++i) {
-        g.t[i] = sh.t[i];
-        g.tn[i] = sh.tn[i];
-        g.tb[i] = sh.tb[i];
-    }
-    for (int i = 0; i < 27; ++i) g.lin[i] = sh.lin[i];
-    g.prev_cost = sh.prev_cost;
-    g.best_cost = sh.best_cost;
-    g.lambda = sh.lambda;
-    g.lr = sh.lr;
-    g.initial_cost = sh.initial_cost;
-    g.gathered = sh.gathered;
-    g.reused = sh.reused;
-    g.best_n = sh.best_n;
-    g.has_best = sh.has_best;
-    g.status = sh.status;
-    g.flag = sh.flag;
-    g.hist_len = sh.hist_len;
-    g.n_evals = sh.n_evals;
-    g.initial_set = sh.initial_set;
-    for (int i = 0; i < FMPNP_MAX_LEVELS; ++i) g.level_status[i] = sh.level_status[i];
+    __threadfence();  // every lane's part before the queue entry that announces the state (enqueue_evaluation, lane 0)
 }
 
 // describes the next evaluation of a query in its global state (thread 0)
@@ -553,6 +568,8 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         c.crank = 0;
         c.part_out = nullptr;
         c.limit_given = false;
+        c.row_pol = p.l2_policy ? l2_policy_evict_first() : l2_policy_normal();
+        c.rec_pol = p.l2_policy ? l2_policy_evict_last() : l2_policy_normal();
         c.c0 = gv.ev_c0;
         c.Cl = gv.ev_Cl;
         c.loss_id = gv.ev_loss;
@@ -662,7 +679,7 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
         // ---- this CTA completed the evaluation: total the query, advance its state machine
         c.n0 = 0;
         c.n1 = q.N;
-        if (tid == 0) load_state(sh, gv);
+        if (warp == 0) load_state(sh, gv, lane);
         __syncthreads();
         if (multi)
             combine_parts(sh, parts, uq);
@@ -670,128 +687,183 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             reduce_points<true>(c, evpose, evpose + 9, sh, rp);
         else
             reduce_points<false>(c, evpose, evpose + 9, sh, rp);
-        if (tid == 0) {
-            if (!(MODE == kModeRefine && c.inl_out != nullptr)) sh.n_evals += 1;  // the inlier pass is not an LM evaluation
-            sh.gathered += (long long)sh.ev_ngath * c.Cl * (grad ? 4 : 2);
-            sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (grad ? 4 : 2);
-        }
-        __syncthreads();
 
-        bool finished = false, have_eval = false;
-        int lvl = gv.level, it = gv.it;
-        const int phase = gv.phase;
-        enum { kStartLevel, kTryStep, kFinishLevel, kCostEval } next = kStartLevel;
-
-        if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
-            if (tid == 0) {
-                p.cost_out[qi] = sh.ev_nsup > 0 ? sh.ev_cost : NAN;
-                if (p.nsup_out) p.nsup_out[qi] = sh.ev_nsup;
-            }
-            finished = true;
-        } else if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152): the mask was written by reduce_points
-            finished = true;
-        } else if (phase == kPhaseInliers) {  // the mask is in `inl`: on to compute_cost (pyramid) or level 0
-            lvl = 0;
-            next = p.n_levels > 0 ? kCostEval : kStartLevel;
-        } else if (phase == kPhaseCost) {
-            if (sh.ev_nsup == 0) {  // compute_cost is None -> return the initial pose (model.py:183-187)
-                if (tid == 0) sh.status = FMPNP_STATUS_NO_INITIAL_COST;
-                finished = true;
-            } else {
-                if (tid == 0) {
-                    sh.initial_cost = sh.ev_cost;
-                    sh.initial_set = 1;
-                }
-                lvl = 0;
-                next = kStartLevel;
-            }
-        } else if (phase == kPhaseFirst) {  // i == 0 of a level (model.py:303-359)
-            if (sh.ev_nsup == 0) {          // model.py:316-320 -> forward returns the CURRENT pose
-                if (tid == 0) {
-                    sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
-                    sh.level_status[lvl] = FMPNP_STATUS_EMPTY_SUPPORT;
-                }
-                ++lvl;
-                next = kStartLevel;
-                finished = lvl >= (p.n_levels > 0 ? p.n_levels : 1);
-            } else {
-                if (tid == 0) {
-                    lm_first_evaluation(sh, p, qi);
-                }
-                it = 0;
-                next = kTryStep;
-            }
-        } else {  // trial pose evaluated (model.py:428-486)
-            if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
-                if (tid == 0) {
-                    sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
-                    sh.flag = 2;
-                }
-                next = kFinishLevel;
-            } else {
-                if (tid == 0) {
-                    lm_trial_evaluation(sh, p, qi);
-                }
-                ++it;
-                next = kTryStep;
-            }
-        }
-
+        int lvl = gv.level, it = gv.it, phase = gv.phase;
+        bool ev_grad = grad;
         const int nlev = p.n_levels > 0 ? p.n_levels : 1;
-        while (!finished && !have_eval) {
+        // Owner loop: the evaluations that follow are run right here, without the task queue, for as long as they are
+        // expected to be light (LaunchParams::light); otherwise the next evaluation is described in the query's global
+        // state and queued, and the loop is left after one pass.
+        for (;;) {
+            if (tid == 0) {
+                if (!(MODE == kModeRefine && phase == kPhaseInliers)) sh.n_evals += 1;  // the inlier pass is not an LM evaluation
+                sh.gathered += (long long)sh.ev_ngath * c.Cl * (ev_grad ? 4 : 2);
+                sh.reused += (long long)(sh.ev_nsup - sh.ev_ngath) * c.Cl * (ev_grad ? 4 : 2);
+            }
             __syncthreads();
-            if (next == kCostEval) {  // multilevel: compute_cost on ALL channels (model.py:182), on the inliers
-                if (tid == 0)
-                    describe_evaluation(g, sh.R, sh.t, kPhaseCost, 0, 0, q.C, p.use_ratio ? 2 : 0, FMPNP_LOSS_SQUARED, -1, uq);
-                have_eval = true;
-            } else if (next == kStartLevel) {
+
+            bool finished = false, have_eval = false;
+            enum { kStartLevel, kTryStep, kFinishLevel, kCostEval } next = kStartLevel;
+            // the evaluation that comes next (uniform across the CTA): phase, rows, slice, ratio mode, loss, pose
+            int nd_phase = kPhaseCost, nd_grad = 0, nd_c0 = 0, nd_Cl = q.C, nd_ratio = 0, nd_loss = p.loss_id;
+            bool nd_hist = false, nd_trial_pose = false;
+
+            if (MODE == kModeComputeCost) {  // sparseFeaturePnP.compute_cost (model.py:216-243)
                 if (tid == 0) {
-                    const int c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
-                    const int Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
-                    describe_evaluation(g, sh.R, sh.t, kPhaseFirst, 1, c0, Cl, p.use_ratio ? 1 : 0, p.loss_id, sh.hist_len,
-                                        uq);
+                    p.cost_out[qi] = sh.ev_nsup > 0 ? sh.ev_cost : NAN;
+                    if (p.nsup_out) p.nsup_out[qi] = sh.ev_nsup;
                 }
-                have_eval = true;
-            } else if (next == kTryStep) {
-                if (it >= p.n_iters) {
+                finished = true;
+            } else if (MODE == kModeFindInliers) {  // find_inliers (model.py:131-152): the mask was written by reduce_points
+                finished = true;
+            } else if (phase == kPhaseInliers) {  // the mask is in `inl`: on to compute_cost (pyramid) or level 0
+                lvl = 0;
+                next = p.n_levels > 0 ? kCostEval : kStartLevel;
+            } else if (phase == kPhaseCost) {
+                if (sh.ev_nsup == 0) {  // compute_cost is None -> return the initial pose (model.py:183-187)
+                    if (tid == 0) sh.status = FMPNP_STATUS_NO_INITIAL_COST;
+                    finished = true;
+                } else {
+                    if (tid == 0) {
+                        sh.initial_cost = sh.ev_cost;
+                        sh.initial_set = 1;
+                    }
+                    lvl = 0;
+                    next = kStartLevel;
+                }
+            } else if (phase == kPhaseFirst) {  // i == 0 of a level (model.py:303-359)
+                if (sh.ev_nsup == 0) {          // model.py:316-320 -> forward returns the CURRENT pose
+                    if (tid == 0) {
+                        sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                        sh.level_status[lvl] = FMPNP_STATUS_EMPTY_SUPPORT;
+                    }
+                    ++lvl;
+                    next = kStartLevel;
+                    finished = lvl >= nlev;
+                } else {
+                    if (tid == 0) {
+                        lm_first_evaluation(sh, p, qi);
+                    }
+                    it = 0;
+                    next = kTryStep;
+                }
+            } else {  // trial pose evaluated (model.py:428-486)
+                if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
+                    if (tid == 0) {
+                        sh.status = FMPNP_STATUS_EMPTY_SUPPORT;
+                        sh.flag = 2;
+                    }
                     next = kFinishLevel;
-                    continue;
+                } else {
+                    if (tid == 0) {
+                        lm_trial_evaluation(sh, p, qi);
+                    }
+                    ++it;
+                    next = kTryStep;
                 }
-                if (warp == 0) solve_and_update(sh, p.solver, lane);
+            }
+
+            while (!finished && !have_eval) {
                 __syncthreads();
-                if (sh.flag == 1) {  // NaN step: leave the loop, best pose (model.py:411-413)
+                if (next == kCostEval) {  // multilevel: compute_cost on ALL channels (model.py:182), on the inliers
+                    nd_phase = kPhaseCost;
+                    nd_grad = 0;
+                    nd_c0 = 0;
+                    nd_Cl = q.C;
+                    nd_ratio = p.use_ratio ? 2 : 0;
+                    nd_loss = FMPNP_LOSS_SQUARED;
+                    nd_hist = false;
+                    nd_trial_pose = false;
+                    have_eval = true;
+                } else if (next == kStartLevel) {
+                    nd_phase = kPhaseFirst;
+                    nd_grad = 1;
+                    nd_c0 = p.n_levels > 0 ? p.levels[lvl][0] : 0;
+                    nd_Cl = p.n_levels > 0 ? p.levels[lvl][1] - p.levels[lvl][0] : q.C;
+                    nd_ratio = p.use_ratio ? 1 : 0;
+                    nd_loss = p.loss_id;
+                    nd_hist = true;
+                    nd_trial_pose = false;
+                    have_eval = true;
+                } else if (next == kTryStep) {
+                    if (it >= p.n_iters) {
+                        next = kFinishLevel;
+                        continue;
+                    }
+                    if (warp == 0) solve_and_update(sh, p.solver, lane);
                     __syncthreads();
-                    if (tid == 0) sh.status = FMPNP_STATUS_NAN_STEP;
-                    next = kFinishLevel;
-                    continue;
+                    if (sh.flag == 1) {  // NaN step: leave the loop, best pose (model.py:411-413)
+                        __syncthreads();
+                        if (tid == 0) sh.status = FMPNP_STATUS_NAN_STEP;
+                        next = kFinishLevel;
+                        continue;
+                    }
+                    nd_phase = kPhaseTrial;
+                    nd_grad = 1;
+                    nd_c0 = c.c0;  // the level's slice: a trial evaluation follows an evaluation of the same level
+                    nd_Cl = c.Cl;
+                    nd_ratio = p.use_ratio ? 1 : 0;
+                    nd_loss = p.loss_id;
+                    nd_hist = true;
+                    nd_trial_pose = true;
+                    have_eval = true;
+                } else {  // kFinishLevel (model.py:491-494): best pose unless the loop was left on an empty support
+                    if (tid == 0) {
+                        lm_finish_level(sh, lvl);
+                    }
+                    ++lvl;
+                    next = kStartLevel;
+                    finished = lvl >= nlev;
                 }
-                if (tid == 0)
-                    describe_evaluation(g, sh.Rn, sh.tn, kPhaseTrial, 1, gv.ev_c0, gv.ev_Cl, p.use_ratio ? 1 : 0, p.loss_id,
-                                        sh.hist_len, uq);
-                have_eval = true;
-            } else {  // kFinishLevel (model.py:491-494): best pose unless the loop was left on an empty support
-                if (tid == 0) {
-                    lm_finish_level(sh, lvl);
-                }
-                ++lvl;
-                next = kStartLevel;
-                finished = lvl >= nlev;
             }
-        }
-        __syncthreads();
-        if (tid == 0) {
+            __syncthreads();
             if (finished) {
-                if (MODE == kModeRefine) {
-                    write_result(sh, p, qi);
+                if (tid == 0) {
+                    if (MODE == kModeRefine) {
+                        write_result(sh, p, qi);
+                    }
+                    __threadfence();
+                    atomicAdd(sc.done, 1u);
                 }
-                __threadfence();
-                atomicAdd(sc.done, 1u);
-            } else {
-                store_state(sh, g);
-                g.level = lvl;
-                g.it = it;
-                enqueue_evaluation(sc, qi, uq);
+                break;
             }
+            // light: a trial evaluation, or the first evaluation of the only level right after an inlier pass that left
+            // its records (every tag matches) -- records are reused and nearly all of them are in place
+            const bool light = MODE == kModeRefine && p.light != 0 && p.reuse != 0 &&
+                               (nd_phase == kPhaseTrial ||
+                                (nd_phase == kPhaseFirst && phase == kPhaseInliers && p.n_levels == 0));
+            if (!light) {
+                if (tid == 0) {
+                    describe_evaluation(g, nd_trial_pose ? sh.Rn : sh.R, nd_trial_pose ? sh.tn : sh.t, nd_phase, nd_grad, nd_c0,
+                                        nd_Cl, nd_ratio, nd_loss, nd_hist ? sh.hist_len : -1, uq);
+                    g.level = lvl;
+                    g.it = it;
+                }
+                if (warp == 0) {
+                    store_state(sh, g, lane);
+                    __syncwarp();
+                    if (lane == 0) enqueue_evaluation(sc, qi, uq);
+                }
+                break;
+            }
+            // ---- the next evaluation, here and now: all points of the query, this CTA alone
+            c.c0 = nd_c0;
+            c.Cl = nd_Cl;
+            c.loss_id = nd_loss;
+            c.ratio_mode = nd_ratio;
+            c.thr = p.ratio_thr;
+            c.inl_out = nullptr;
+            c.active = p.inlier_on ? p.inl + (size_t)qi * p.n_max : q.active;
+            c.reuse_gen = p.reuse_base + (uint32_t)(qi * nlev + lvl);
+            c.aligned = slice_aligned(q, c.c0, c.Cl, true);
+            c.csize = 1;
+            c.crank = 0;
+            c.part_out = nullptr;
+            c.limit_given = false;
+            hist_slices(p, qi, sh.hist_len, c);
+            light_evaluate(c, nd_trial_pose ? sh.Rn : sh.R, nd_trial_pose ? sh.tn : sh.t, sh, rp);
+            phase = nd_phase;
+            ev_grad = true;
         }
     }
 }

@@ -16,7 +16,9 @@ constexpr int kRanges = 128;                      // max fixed reduction ranges 
 constexpr int kMinRanges = 16;                    // min (small queries) == max cluster size
 constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
 constexpr int kLaneStride = 33;                   // reduction scratch: doubles per transposed row (conflict-free columns)
-constexpr int kWarpScratchDoubles = 28 * kLaneStride + 8 * 28;  // per warp: transposition + pairwise-tree stack
+constexpr int kHalfSums = 14;                     // the 28 sums of a range are transposed in two rounds of 14
+constexpr int kWarpScratchDoubles = kHalfSums * kLaneStride + 8 * 28;  // per warp: transposition + pairwise-tree stack
+constexpr int kMinRingPerWarp = (kWarpScratchDoubles * 8 + 127) & ~127;  // bytes of ring a warp needs as reduction scratch
 constexpr int kMaxDepth = 8;                      // max slots per sub-ring
 
 enum KernelMode { kModeRefine = 0, kModeComputeCost = 1, kModeFindInliers = 2 };
@@ -122,6 +124,12 @@ struct LaunchParams {
     int32_t inlier_on;
     double inlier_thr;
     uint32_t reuse_base;    // first generation of this launch (never 0)
+    // Light evaluations (fmpnp_light.cuh): with record reuse, an evaluation after the first one of a level finds nearly
+    // every record in place.  1: such an evaluation is run as a whole by the CTA that completed the previous evaluation
+    // of the query -- the LM state stays in shared memory, nothing goes through the task queue -- with the latency-
+    // oriented light_evaluate(); 0: every evaluation takes the general route.  Same bits either way.
+    int32_t light;
+    int32_t l2_policy;      // 1: gathered rows evict_first, staged records evict_last in L2; 0: no preference
 };
 
 // Host-side launchers (defined in fmpnp_kernels.cu)

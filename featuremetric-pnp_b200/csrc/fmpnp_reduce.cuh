@@ -131,66 +131,143 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
     const int rpw = nr >= kWarps ? nr / kWarps : 1;  // consecutive ranges per warp ...
     const int wact = nr >= kWarps ? kWarps : nr;     // ... of the warps that own any
     double* const wscr = reinterpret_cast<double*>(c.ring + (size_t)warp * c.ring_per_warp);  // idle ring slice
-    double* const stack = wscr + 28 * kLaneStride;
+    double* const stack = wscr + kHalfSums * kLaneStride;
     int32_t cnt[3] = {0, 0, 0};  // survivors, supported, supported and gathered by this evaluation (this lane, all its ranges)
+    // Staging (with gradients, when the warp's ring slice has room beside the reduction scratch): what the per-point
+    // phase reads of a point -- record (48 B) and coordinates (24 B); the addresses depend on n only -- is copied into
+    // the idle part of the slice with cp.async one row of 32 points AHEAD, so the L2 round trip is behind the arithmetic
+    // and the transposition of the current row instead of in front of them, and no register holds data in flight.
+    // Every lane copies and reads its own point only: its own wait_group is all the synchronisation this needs.
+    constexpr int kRowRec = 32 * 48, kRowBytes = kRowRec + 32 * 24;
+    const bool stage = GRAD && c.ring_per_warp >= kMinRingPerWarp + 2 * kRowBytes;
+    const uint32_t sbuf = smem_u32(wscr) + (uint32_t)kMinRingPerWarp;
+    const int rows_pr = (per + 31) >> 5;  // rows of 32 points per range
+    const int rbase = r_first + warp * rpw;
+    auto point_of = [&](int rr, int j) -> int {
+        const int r0 = min(q.N, (rbase + rr) * per), r1 = min(q.N, r0 + per);
+        const int n = r0 + 32 * j + lane;
+        return n < r1 ? n : -1;
+    };
+    auto issue_row = [&](int n, int buf) {  // one commit group per row (empty for a lane without a point in it)
+        if (n >= 0) {
+            const char* r = reinterpret_cast<const char*>(c.rec + (size_t)n * kRecDoubles);
+            const uint32_t d = sbuf + (uint32_t)(buf * kRowBytes + lane * 48);
+            cp_async16_pol(d, r, c.rec_pol);
+            cp_async16_pol(d + 16, r + 16, c.rec_pol);
+            cp_async16_pol(d + 32, r + 32, c.rec_pol);
+            const char* pt = reinterpret_cast<const char*>(q.pts + 3 * (size_t)n);
+            const uint32_t e = sbuf + (uint32_t)(buf * kRowBytes + kRowRec + lane * 24);
+            cp_async8_s(e, pt);
+            cp_async8_s(e + 8, pt + 8);
+            cp_async8_s(e + 16, pt + 16);
+        }
+        cp_async_commit();
+    };
     if (warp < wact) {
+        int buf = 0;
+        uint8_t flag_nx = 0;
+        if (stage) {
+            const int n0 = point_of(0, 0);
+            issue_row(n0, 0);
+            if (n0 >= 0) flag_nx = __ldcg(c.supp + n0);
+        }
         for (int rr = 0; rr < rpw; ++rr) {
-            const int r0 = min(q.N, (r_first + warp * rpw + rr) * per), r1 = min(q.N, r0 + per);
+            const int r0 = min(q.N, (rbase + rr) * per), r1 = min(q.N, r0 + per);
             double acc[28];
 #pragma unroll
             for (int i = 0; i < 28; ++i) acc[i] = 0.0;
-            for (int n = r0 + lane; n < r1; n += 32) {
-                // flag, record and point are loaded side by side (their addresses depend on n only): one L2 round
-                // trip per point instead of three; what an unsupported point's record holds is never used
-                const uint8_t sflag = __ldcg(c.supp + n);
-                const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
-                const double2 rc0 = __ldcg(r);
-                double2 rc1 = make_double2(0.0, 0.0), rc2 = rc1;
-                double ptx = 0.0, pty = 0.0, ptz = 0.0;
-                if (GRAD) {
-                    rc1 = __ldcg(r + 1);
-                    rc2 = __ldcg(r + 2);
-                    ptx = q.pts[3 * n];
-                    pty = q.pts[3 * n + 1];
-                    ptz = q.pts[3 * n + 2];
-                }
-                const bool sup = sflag != 0;
-                bool keep = false;
-                if (sup) {
-                    ++cnt[1];
-                    cnt[2] += sflag == 1;
-                    const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
-                    double rho = x, w = 1.0;
-                    if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
-                    keep = !use_ratio || (fabs(rho) < limit);
-                    if (keep) {
-                        ++cnt[0];
-                        acc[27] = __dadd_rn(acc[27], rho);
-                        if (GRAD) {
-                            const Proj pr = project_point(R, t, q.K, ptx, pty, ptz, q.im_w, q.im_h);
-                            contract_point(fx, fy, pr.X, pr.Y, pr.Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
-                        }
+            for (int j = 0; j < rows_pr; ++j, buf ^= 1) {
+                const int n = r0 + 32 * j + lane;
+                const bool has = n < r1;
+                uint8_t sflag = flag_nx;
+                if (stage) {
+                    int nrr = rr, nj = j + 1;
+                    if (nj == rows_pr) {
+                        nj = 0;
+                        ++nrr;
+                    }
+                    if (nrr < rpw) {  // uniform
+                        const int nn = point_of(nrr, nj);
+                        issue_row(nn, buf ^ 1);
+                        if (nn >= 0) flag_nx = __ldcg(c.supp + nn);
+                        cp_async_wait_pending(1);
+                    } else {
+                        cp_async_wait_pending(0);
                     }
                 }
-                if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
-                if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
-            }
-            // the 32 lane partials of each of the 28 sums -> lane i (transposition), pairwise tree over the lanes
-            __syncwarp();  // the rows of the previous range have been read
-#pragma unroll
-            for (int i = 0; i < 28; ++i) wscr[i * kLaneStride + lane] = acc[i];
-            __syncwarp();
-            if (lane < 28) {
-                const double* row = wscr + lane * kLaneStride;
-                double x[16];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) x[k] = __dadd_rn(row[2 * k], row[2 * k + 1]);
-#pragma unroll
-                for (int w = 1; w < 16; w <<= 1) {
-#pragma unroll
-                    for (int k = 0; k + w < 16; k += 2 * w) x[k] = __dadd_rn(x[k], x[k + w]);
+                if (has) {
+                    // flag, record and point: from the staged row, or loaded side by side (one L2 round trip per point;
+                    // .cg: flags and records may have been written by another CTA); what an unsupported point's record
+                    // holds is never used
+                    double2 rc0, rc1 = make_double2(0.0, 0.0), rc2 = rc1;
+                    double ptx = 0.0, pty = 0.0, ptz = 0.0;
+                    if (stage) {
+                        const uint32_t d = sbuf + (uint32_t)(buf * kRowBytes + lane * 48);
+                        rc0 = lds128d(d);
+                        rc1 = lds128d(d + 16);
+                        rc2 = lds128d(d + 32);
+                        const uint32_t e = sbuf + (uint32_t)(buf * kRowBytes + kRowRec + lane * 24);
+                        ptx = lds64d(e);
+                        pty = lds64d(e + 8);
+                        ptz = lds64d(e + 16);
+                    } else {
+                        sflag = __ldcg(c.supp + n);
+                        const double2* r = reinterpret_cast<const double2*>(c.rec + (size_t)n * kRecDoubles);
+                        rc0 = __ldcg(r);
+                        if (GRAD) {
+                            rc1 = __ldcg(r + 1);
+                            rc2 = __ldcg(r + 2);
+                            ptx = q.pts[3 * n];
+                            pty = q.pts[3 * n + 1];
+                            ptz = q.pts[3 * n + 2];
+                        }
+                    }
+                    const bool sup = sflag != 0;
+                    bool keep = false;
+                    if (sup) {
+                        ++cnt[1];
+                        cnt[2] += sflag == 1;
+                        const double x = __dmul_rn(0.5, rc0.x);  // cost = 0.5 * sum e^2 (model.py:338)
+                        double rho = x, w = 1.0;
+                        if (c.ratio_mode != 2) robust_loss(c.loss_id, c.alpha, x, rho, w);
+                        keep = !use_ratio || (fabs(rho) < limit);
+                        if (keep) {
+                            ++cnt[0];
+                            acc[27] = __dadd_rn(acc[27], rho);
+                            if (GRAD) {
+                                double X, Y, Z;
+                                transform_point(R, t, ptx, pty, ptz, X, Y, Z);
+                                contract_point(fx, fy, X, Y, Z, w, rc0.y, rc1.x, rc1.y, rc2.x, rc2.y, acc);
+                            }
+                        }
+                    }
+                    if (c.h_kept) c.h_kept[n] = keep ? 1 : 0;
+                    if (c.inl_out) c.inl_out[n] = keep ? 1 : 0;
                 }
-                double tot = x[0];
+            }
+            // the 32 lane partials of each of the 28 sums -> lane i (transposition, two rounds of 14 sums through the
+            // same scratch), pairwise tree over the lanes
+            double tot = 0.0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                __syncwarp();  // the rows of the previous round / range have been read
+#pragma unroll
+                for (int i = 0; i < kHalfSums; ++i) wscr[i * kLaneStride + lane] = acc[h * kHalfSums + i];
+                __syncwarp();
+                if (lane >= h * kHalfSums && lane < (h + 1) * kHalfSums) {
+                    const double* row = wscr + (lane - h * kHalfSums) * kLaneStride;
+                    double x[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) x[k] = __dadd_rn(row[2 * k], row[2 * k + 1]);
+#pragma unroll
+                    for (int w = 1; w < 16; w <<= 1) {
+#pragma unroll
+                        for (int k = 0; k + w < 16; k += 2 * w) x[k] = __dadd_rn(x[k], x[k + w]);
+                    }
+                    tot = x[0];
+                }
+            }
+            if (lane < 28) {
                 int level = 0;
                 for (int kk = rr; kk & 1; kk >>= 1) {  // binary-counter stack: pairwise tree over this warp's ranges
                     tot = __dadd_rn(stack[level * 28 + lane], tot);

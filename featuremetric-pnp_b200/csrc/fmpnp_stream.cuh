@@ -74,6 +74,7 @@ struct EvalCtx {
     int32_t csize, crank;              // thread-block cluster working on this query (or: tasks of this evaluation)
     double* part_out;                  // task scheduler: this task's partial sums go here (global), no combine
     bool limit_given;                  // task scheduler: sh.limit already holds the ratio-test limit
+    uint64_t row_pol, rec_pol;         // L2 policies: gathered rows (read once), staged records / coordinates (read again)
 };
 
 // Staging geometry of one evaluation.
@@ -275,24 +276,27 @@ __device__ __forceinline__ void acc4(uint32_t aF, uint32_t aGx, uint32_t aGy, ui
 __device__ __forceinline__ int batch_width(int span) { return span > 128 ? 32 : (span > 64 ? 16 : (span > 32 ? 8 : 4)); }
 
 template <int ROWS, int FULL>
-__device__ __forceinline__ void copy_rows_full(uint32_t dst, const char* const (&s)[4], uint32_t rowB) {
+__device__ __forceinline__ void copy_rows_full(uint32_t dst, const char* const (&s)[4], uint32_t rowB, uint64_t pol) {
 #pragma unroll
     for (int r = 0; r < ROWS; ++r) {
         const uint32_t d = dst + (uint32_t)r * rowB;
         const char* g = s[r];
-        if (FULL > 0) cp_async16_off<0>(d, g);
-        if (FULL > 1) cp_async16_off<512>(d, g);
-        if (FULL > 2) cp_async16_off<1024>(d, g);
-        if (FULL > 3) cp_async16_off<1536>(d, g);
-        if (FULL > 4) cp_async16_off<2048>(d, g);
-        if (FULL > 5) cp_async16_off<2560>(d, g);
-        if (FULL > 6) cp_async16_off<3072>(d, g);
-        if (FULL > 7) cp_async16_off<3584>(d, g);
+        if (FULL > 0) cp_async16_pol_off<0>(d, g, pol);
+        if (FULL > 1) cp_async16_pol_off<512>(d, g, pol);
+        if (FULL > 2) cp_async16_pol_off<1024>(d, g, pol);
+        if (FULL > 3) cp_async16_pol_off<1536>(d, g, pol);
+        if (FULL > 4) cp_async16_pol_off<2048>(d, g, pol);
+        if (FULL > 5) cp_async16_pol_off<2560>(d, g, pol);
+        if (FULL > 6) cp_async16_pol_off<3072>(d, g, pol);
+        if (FULL > 7) cp_async16_pol_off<3584>(d, g, pol);
     }
 }
 
+// list_cnt >= 0: the warp's supported points are already in its buffer 0 (Shared::bl_cell / bl_n, list_cnt entries: the
+// points a light evaluation found without a valid record, fmpnp_light.cuh) -- nothing is projected, that one batch is
+// streamed.
 template <bool GRAD, int LOG2L>
-__device__ void stream_staged(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
+__device__ void stream_staged(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp, int list_cnt = -1) {
     constexpr int ROWS = GRAD ? 4 : 2;
     constexpr int L = 1 << LOG2L, G = 32 / L;
     constexpr bool SHORT = LOG2L < 5;  // several points per item, at most 2 float4 of a row per lane
@@ -306,9 +310,10 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
     const int32_t* bn = &sh.bl_n[warp][0][0];
     // batches of BW points owned by this warp: base = n0 + (warp + b * kWarps) * BW.  BW = 32 unless the CTA
     // has so few points (a small task of the scheduler) that narrower batches are needed to occupy every warp.
+    const bool list = list_cnt >= 0;
     const int BW = batch_width(N - c.n0);
     const int first = c.n0 + warp * BW;
-    const int nb = first < N ? (N - first + kWarps * BW - 1) / (kWarps * BW) : 0;
+    const int nb = list ? (list_cnt > 0 ? 1 : 0) : (first < N ? (N - first + kWarps * BW - 1) / (kWarps * BW) : 0);
     if (nb == 0) return;
 
     // row base pointers with this lane's 16-byte piece folded in
@@ -317,6 +322,7 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
     const char* baseGy = GRAD ? reinterpret_cast<const char*>(q.Gy + c.c0) + lane * 16 : nullptr;
     const char* baseR = reinterpret_cast<const char*>(q.ref + c.c0) + lane * 16;
     const uint32_t pitch = (uint32_t)q.C * 4u;  // bytes between rows of a map / of ref
+    const uint64_t pol = c.row_pol;             // L2 policy of the row copies (read once: evict_first)
 
     // projects batch b and leaves its supported points compacted in buffer `buf`; returns their count
     auto load_batch = [&](int b, int buf) -> int {
@@ -359,21 +365,21 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
         if (SHORT) {  // nv <= 32: one 16-byte piece of every row per lane
             if (lane < nv) {
 #pragma unroll
-                for (int r = 0; r < ROWS; ++r) cp_async16_s(dst + (uint32_t)(r * nv) * 16u, s[r]);
+                for (int r = 0; r < ROWS; ++r) cp_async16_pol(dst + (uint32_t)(r * nv) * 16u, s[r], pol);
             }
             return;
         }
         if (tail == 0 && full <= 8) {  // the usual case: immediate offsets, no loop
             const uint32_t rowB = (uint32_t)nv * 16u;
             switch (full) {
-                case 1: copy_rows_full<ROWS, 1>(dst, s, rowB); break;
-                case 2: copy_rows_full<ROWS, 2>(dst, s, rowB); break;
-                case 3: copy_rows_full<ROWS, 3>(dst, s, rowB); break;
-                case 4: copy_rows_full<ROWS, 4>(dst, s, rowB); break;
-                case 5: copy_rows_full<ROWS, 5>(dst, s, rowB); break;
-                case 6: copy_rows_full<ROWS, 6>(dst, s, rowB); break;
-                case 7: copy_rows_full<ROWS, 7>(dst, s, rowB); break;
-                default: copy_rows_full<ROWS, 8>(dst, s, rowB); break;
+                case 1: copy_rows_full<ROWS, 1>(dst, s, rowB, pol); break;
+                case 2: copy_rows_full<ROWS, 2>(dst, s, rowB, pol); break;
+                case 3: copy_rows_full<ROWS, 3>(dst, s, rowB, pol); break;
+                case 4: copy_rows_full<ROWS, 4>(dst, s, rowB, pol); break;
+                case 5: copy_rows_full<ROWS, 5>(dst, s, rowB, pol); break;
+                case 6: copy_rows_full<ROWS, 6>(dst, s, rowB, pol); break;
+                case 7: copy_rows_full<ROWS, 7>(dst, s, rowB, pol); break;
+                default: copy_rows_full<ROWS, 8>(dst, s, rowB, pol); break;
             }
             return;
         }
@@ -382,8 +388,8 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
             uint32_t d = dst + (uint32_t)(r * nv) * 16u;
             const char* g = s[r];
 #pragma unroll 4
-            for (int i = 0; i < full; ++i, d += 512, g += 512) cp_async16_s(d, g);
-            if (lane < tail) cp_async16_s(d, g);
+            for (int i = 0; i < full; ++i, d += 512, g += 512) cp_async16_pol(d, g, pol);
+            if (lane < tail) cp_async16_pol(d, g, pol);
         }
     };
 
@@ -493,7 +499,7 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
         __syncwarp();  // every lane is done with the slot: it may be refilled
     };
 
-    int cnt0 = load_batch(0, 0), cnt1 = 0;
+    int cnt0 = list ? list_cnt : load_batch(0, 0), cnt1 = 0;
     int ib = 0, ii = 0, cb = 0, ci = 0, inflight = 0;
     int items_i = items_of(cnt0), items_c = items_i;
     for (;;) {
@@ -537,13 +543,34 @@ __device__ void stream_staged(const EvalCtx& c, const double* R, const double* t
     }
 }
 
+// generic path (channel ranges that are not 16-byte aligned): the whole warp loads the rows of one point directly
+template <bool GRAD>
+__device__ __forceinline__ void gather_point_generic(const EvalCtx& c, int cell, int n, int lane) {
+    const QueryDev& q = *c.q;
+    const float* srcF = q.F + (size_t)cell * q.C + c.c0;
+    const float* srcGx = GRAD ? q.Gx + (size_t)cell * q.C + c.c0 : nullptr;
+    const float* srcGy = GRAD ? q.Gy + (size_t)cell * q.C + c.c0 : nullptr;
+    const float* srcR = q.ref + (size_t)n * q.C + c.c0;
+    double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int ch = lane; ch < c.Cl; ch += 32) {
+        const float f = __ldg(srcF + ch), r = __ldg(srcR + ch);
+        float gx = 0.f, gy = 0.f;
+        if (GRAD) {
+            gx = __ldg(srcGx + ch);
+            gy = __ldg(srcGy + ch);
+        }
+        acc1<GRAD>(f, r, gx, gy, a);
+    }
+    reduce_lanes<GRAD, 5>(a);
+    if (lane == 0) write_record<GRAD>(a, c.rec + (size_t)n * kRecDoubles);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Streaming phase: one record per supported point.  Every warp is its own producer and consumer.
 // ---------------------------------------------------------------------------------------------
 template <bool GRAD>
 __device__ void stream_points(const EvalCtx& c, const double* R, const double* t, Shared& sh, RingPos& rp) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const QueryDev& q = *c.q;
     const int N = c.n1;
 
     if (!c.aligned) {
@@ -556,23 +583,7 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
             for (int j = 0; j < BW; ++j) {
                 const int cj = __shfl_sync(0xffffffffu, cell, j);
                 if (cj < 0) continue;
-                const int nj = base + j;
-                const float* srcF = q.F + (size_t)cj * q.C + c.c0;
-                const float* srcGx = GRAD ? q.Gx + (size_t)cj * q.C + c.c0 : nullptr;
-                const float* srcGy = GRAD ? q.Gy + (size_t)cj * q.C + c.c0 : nullptr;
-                const float* srcR = q.ref + (size_t)nj * q.C + c.c0;
-                double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-                for (int ch = lane; ch < c.Cl; ch += 32) {
-                    const float f = __ldg(srcF + ch), r = __ldg(srcR + ch);
-                    float gx = 0.f, gy = 0.f;
-                    if (GRAD) {
-                        gx = __ldg(srcGx + ch);
-                        gy = __ldg(srcGy + ch);
-                    }
-                    acc1<GRAD>(f, r, gx, gy, a);
-                }
-                reduce_lanes<GRAD, 5>(a);
-                if (lane == 0) write_record<GRAD>(a, c.rec + (size_t)nj * kRecDoubles);
+                gather_point_generic<GRAD>(c, cj, base + j, lane);
             }
         }
         return;
@@ -583,6 +594,23 @@ __device__ void stream_points(const EvalCtx& c, const double* R, const double* t
         case 8: stream_staged<GRAD, 3>(c, R, t, sh, rp); break;
         case 16: stream_staged<GRAD, 4>(c, R, t, sh, rp); break;
         default: stream_staged<GRAD, 5>(c, R, t, sh, rp); break;
+    }
+}
+
+// Streams the `cnt` (<= 32) points this warp has listed in its buffer 0 (cell, index): the rows of the points a light
+// evaluation found without a valid record.  Called by whole warps, independently of each other.
+__device__ void stream_list(const EvalCtx& c, Shared& sh, RingPos& rp, int cnt) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (cnt <= 0) return;
+    if (!c.aligned) {
+        for (int j = 0; j < cnt; ++j) gather_point_generic<true>(c, sh.bl_cell[warp][0][j], sh.bl_n[warp][0][j], lane);
+        return;
+    }
+    switch (c.L) {
+        case 4: stream_staged<true, 2>(c, nullptr, nullptr, sh, rp, cnt); break;
+        case 8: stream_staged<true, 3>(c, nullptr, nullptr, sh, rp, cnt); break;
+        case 16: stream_staged<true, 4>(c, nullptr, nullptr, sh, rp, cnt); break;
+        default: stream_staged<true, 5>(c, nullptr, nullptr, sh, rp, cnt); break;
     }
 }
 
