@@ -203,9 +203,13 @@ struct Geometry {
     int grid, ring_bytes, ring_per_warp, min_depth, cluster, units;
 };
 
-// Light evaluations are run as a whole by one CTA: worth it when there are enough queries to keep the CTAs busy that way
-// (otherwise an evaluation is better cut into tasks; same bits either way)
-bool light_route(const fmpnp_ctx* ctx, int32_t B) { return ctx->light >= 0 ? ctx->light != 0 : (int64_t)B * 2 >= ctx->sm_count; }
+// Light evaluations (fmpnp_light.cuh) are run as a whole by one CTA.  Worth it when there are enough queries to keep the
+// CTAs busy that way AND the evaluation has a ratio test (cut into tasks it needs two rounds through the queue: the
+// limit is a maximum over all points); without one, tasks keep every CTA slot busy and measure faster
+// (profiles/r02/light_route.md).  Same bits either way.
+bool light_route(const fmpnp_ctx* ctx, int32_t B, bool ratio) {
+    return ctx->light >= 0 ? ctx->light != 0 : (ratio && (int64_t)B * 2 >= ctx->sm_count);
+}
 
 int32_t max_points(const fmpnp_problem* probs, int32_t B) {
     int32_t n_max = 1;
@@ -214,10 +218,10 @@ int32_t max_points(const fmpnp_problem* probs, int32_t B) {
     return n_max;
 }
 
-int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g, bool reuse = false) {
+int geometry(fmpnp_ctx* ctx, int32_t B, int32_t n_max, int requested_cluster, Geometry* g, bool reuse = false, bool ratio = false) {
     // the light evaluations of a launch with record reuse take their own route (LaunchParams::light): the tasks are then
     // sized for the evaluations that gather
-    if (reuse && light_route(ctx, B)) reuse = false;
+    if (reuse && light_route(ctx, B, ratio)) reuse = false;
     int ring = ctx->ring_bytes, d = ctx->depth, per_sm = ctx->ctas_per_sm;
     int S = requested_cluster > 0 ? requested_cluster : ctx->cluster;
     // Task scheduler (default): an evaluation is cut into U tasks so that about three tasks per CTA slot are
@@ -463,7 +467,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     FMPNP_CUDA(ctx, cudaSetDevice(ctx->device));
     if (int rc0 = order_after_previous(ctx, stream)) return rc0;
     Geometry g;
-    int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g, ctx->reuse != 0 && o->gather_every_row == 0);
+    int rc = geometry(ctx, B, max_points(probs, B), o->cluster_size, &g, ctx->reuse != 0 && o->gather_every_row == 0, !std::isnan(o->ratio_threshold));
     if (rc) return rc;
     int32_t n_max;
     rc = stage(ctx, probs, B, g.units > 0 ? B : g.grid, &n_max, stream);
@@ -491,7 +495,7 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     lp.solver = o->solver;
     lp.results = results;
     lp.reuse = (ctx->reuse != 0 && o->gather_every_row == 0) ? 1 : 0;
-    lp.light = lp.reuse && g.cluster == 1 && light_route(ctx, B) ? 1 : 0;
+    lp.light = lp.reuse && g.cluster == 1 && light_route(ctx, B, lp.use_ratio != 0) ? 1 : 0;
     lp.inlier_on = (o->inlier_threshold == o->inlier_threshold && o->inlier_threshold != 0.0) ? 1 : 0;  // 0 / NaN = off
     lp.inlier_thr = o->inlier_threshold;
     {  // one generation per (query, level) of this launch; generations are never handed out twice

@@ -24,8 +24,9 @@ struct Proj {
 };
 
 __device__ __forceinline__ int32_t cast_i32_x86(double r) {
-    if (!(r > -2147483649.0 && r < 2147483648.0)) return INT32_MIN;
-    return (int32_t)r;
+    // cvt.rzi.s32.f64 saturates: everything at or below -2^31 already gives INT32_MIN; what is left to redirect are the
+    // values at or above 2^31 (would saturate to INT32_MAX) and NaN (would give 0) -- one comparison that both fail
+    return r < 2147483648.0 ? __double2int_rz(r) : INT32_MIN;
 }
 
 // P = R X + t alone (the same multiply / add chain as in project_point)
@@ -73,9 +74,37 @@ __device__ __forceinline__ int32_t cell_index(int32_t px, int32_t py, int32_t Hf
     return row * Wf + col;
 }
 
+// The usual case, image = 2^k x feature map along an axis: x * f / (f << k) == x >> k for every non-negative x, a shift
+// instead of a ~20-instruction division.  cell_shift returns k, or -1 when the axis needs the division; the callers
+// compute it once per evaluation (it is uniform across a query).
+__device__ __forceinline__ int32_t cell_shift(int32_t im, int32_t f) {
+    const uint32_t k = (uint32_t)im / (uint32_t)f;
+    if (k == 0u || k * (uint32_t)f != (uint32_t)im || (k & (k - 1u)) != 0u) return -1;
+    return 31 - __clz((int)k);
+}
+__device__ __forceinline__ int32_t cell_index_shifted(int32_t px, int32_t py, int32_t Hf, int32_t Wf, int32_t im_w, int32_t im_h,
+                                                      int32_t sx, int32_t sy) {
+    if (sx >= 0 && sy >= 0) return (int32_t)(((uint32_t)py >> sy) * (uint32_t)Wf + ((uint32_t)px >> sx));
+    return cell_index(px, py, Hf, Wf, im_w, im_h);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Robust losses (featurePnP/helpers/utils.py:15-78): x = 0.5 * ||e||^2  ->  (rho, w = rho')
 // ---------------------------------------------------------------------------------------------
+// pow(b, e) for the exponents the common losses produce, as correctly rounded products / divisions / square roots
+// instead of a pow() call (~200 instructions): Geman-McClure (alpha = -2) needs b^-1 and b^-2 per point.  The reference
+// calls torch.pow(tensor, tensor) (utils.py:67-68; SLEEF, 1 ulp); these forms are within 1 ulp of the same value, like
+// CUDA's pow() they replace (costs are compared at 1e-9 relative, masks only move at exact ties).
+__device__ __forceinline__ double pow_scalar(double b, double e) {
+    if (e == -1.0) return 1.0 / b;
+    if (e == -2.0) return 1.0 / __dmul_rn(b, b);
+    if (e == 2.0) return __dmul_rn(b, b);
+    if (e == 3.0) return __dmul_rn(__dmul_rn(b, b), b);
+    if (e == 0.5) return sqrt(b);
+    if (e == -0.5) return 1.0 / sqrt(b);
+    return pow(b, e);
+}
+
 __device__ __forceinline__ void robust_loss(int loss_id, double alpha, double x, double& rho, double& w) {
     switch (loss_id) {
         case 0:  // squared_loss :15-17
@@ -104,8 +133,8 @@ __device__ __forceinline__ void robust_loss(int loss_id, double alpha, double x,
         const double beta_safe = fmax(kEpsF32, fabs(__dadd_rn(alpha, -2.0)));
         const double alpha_safe = (alpha >= 0.0 ? 1.0 : -1.0) * fmax(kEpsF32, fabs(alpha));
         const double base = __dadd_rn(x / beta_safe, 1.0);
-        rho = __dmul_rn(__dmul_rn(2.0, beta_safe / alpha_safe), __dadd_rn(pow(base, __dmul_rn(0.5, alpha)), -1.0));
-        w = pow(base, __dadd_rn(__dmul_rn(0.5, alpha), -1.0));
+        rho = __dmul_rn(__dmul_rn(2.0, beta_safe / alpha_safe), __dadd_rn(pow_scalar(base, __dmul_rn(0.5, alpha)), -1.0));
+        w = pow_scalar(base, __dadd_rn(__dmul_rn(0.5, alpha), -1.0));
     }
 }
 

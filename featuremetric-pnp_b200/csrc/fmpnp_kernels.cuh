@@ -15,7 +15,7 @@ constexpr int kRecTagSlot = 6;                    // the record's tag: (generati
 constexpr int kRanges = 128;                      // max fixed reduction ranges per query == max tasks per evaluation
 constexpr int kMinRanges = 16;                    // min (small queries) == max cluster size
 constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
-constexpr int kLaneStride = 33;                   // reduction scratch: doubles per transposed row (conflict-free columns)
+constexpr int kLaneStride = 34;                   // reduction scratch: doubles per transposed row (16-byte aligned rows, conflict-free 128-bit reads)
 constexpr int kHalfSums = 14;                     // the 28 sums of a range are transposed in two rounds of 14
 constexpr int kWarpScratchDoubles = kHalfSums * kLaneStride + 8 * 28;  // per warp: transposition + pairwise-tree stack
 constexpr int kMinRingPerWarp = (kWarpScratchDoubles * 8 + 127) & ~127;  // bytes of ring a warp needs as reduction scratch

@@ -45,6 +45,7 @@ __device__ void light_project(const EvalCtx& c, const double* R, const double* t
     const double* const pts = q.pts;
     const uint8_t* const active = c.active;
     const int32_t im_w = q.im_w, im_h = q.im_h, Hf = q.Hf, Wf = q.Wf;
+    const int32_t sx = cell_shift(im_w, Wf), sy = cell_shift(im_h, Hf);
     const unsigned long long gen = (unsigned long long)c.reuse_gen << 32;
     double K[9];
 #pragma unroll
@@ -165,7 +166,7 @@ __device__ void light_project(const EvalCtx& c, const double* R, const double* t
             int32_t cell = -1;
             bool hit = false;
             if (sup) {
-                cell = cell_index(pr.px, pr.py, Hf, Wf, im_w, im_h);
+                cell = cell_index_shifted(pr.px, pr.py, Hf, Wf, im_w, im_h, sx, sy);
                 // nearest-cell lookup (model.py:74-97): same cell, same slice => the record the point has is the one
                 // this evaluation would compute
                 const long long want = (long long)(gen | (unsigned int)cell);

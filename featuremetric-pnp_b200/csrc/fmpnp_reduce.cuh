@@ -255,10 +255,13 @@ __device__ void reduce_points(const EvalCtx& c, const double* R, const double* t
                 for (int i = 0; i < kHalfSums; ++i) wscr[i * kLaneStride + lane] = acc[h * kHalfSums + i];
                 __syncwarp();
                 if (lane >= h * kHalfSums && lane < (h + 1) * kHalfSums) {
-                    const double* row = wscr + (lane - h * kHalfSums) * kLaneStride;
+                    const double2* row = reinterpret_cast<const double2*>(wscr + (lane - h * kHalfSums) * kLaneStride);
                     double x[16];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) x[k] = __dadd_rn(row[2 * k], row[2 * k + 1]);
+                    for (int k = 0; k < 16; ++k) {
+                        const double2 v = row[k];
+                        x[k] = __dadd_rn(v.x, v.y);
+                    }
 #pragma unroll
                     for (int w = 1; w < 16; w <<= 1) {
 #pragma unroll
