@@ -54,6 +54,7 @@ struct fmpnp_ctx {
     // record reuse: generations handed out so far (tags of `d_rec` hold generation << 32 | cell, never generation 0)
     uint64_t reuse_next = 1;
     int reuse = 1;  // FMPNP_REUSE=0: gather every row at every evaluation, whatever the options say
+    int light_miss_den = 64;  // FMPNP_LIGHT_MISS_DEN: the light route is left while an evaluation gathers more than 1 / this of its points
     int l2_policy = 1;  // FMPNP_L2_POLICY=0: no L2 eviction preference for gathered rows / staged records
     int light = -1;  // FMPNP_LIGHT: 1 / 0 = the light evaluations of a launch with record reuse always / never take their own route (fmpnp_light.cuh); -1 = automatic
     // One workspace per context: a call issued on another stream than the previous one waits for that call's
@@ -310,6 +311,7 @@ void fill_common(LaunchParams& lp, fmpnp_ctx* ctx, int32_t B, int32_t n_max, con
     lp.cluster_size = g.cluster;
     lp.scheduler = g.units > 0 ? 1 : 0;
     lp.l2_policy = ctx->l2_policy;
+    lp.light_miss_den = ctx->light_miss_den;
 }
 
 // Task scheduler workspace: per-query LM states, the task FIFO and its counters; reset on the stream.
@@ -399,6 +401,8 @@ int fmpnp_create(fmpnp_ctx** out, int device) {
     ctx->reuse = env_int("FMPNP_REUSE", 1);
     ctx->light = env_int("FMPNP_LIGHT", -1);
     ctx->l2_policy = env_int("FMPNP_L2_POLICY", 1) != 0 ? 1 : 0;
+    ctx->light_miss_den = env_int("FMPNP_LIGHT_MISS_DEN", 64);
+    if (ctx->light_miss_den < 1) ctx->light_miss_den = 1;
     {  // fmpnp_compute_cost_batch_noalloc: resolve its scratch array now, so that the call itself only launches
         void* scratch = nullptr;
         if (static_scratch_setup(device, kNoallocRingBytes, &scratch) != cudaSuccess) cudaGetLastError();  // reported by the call

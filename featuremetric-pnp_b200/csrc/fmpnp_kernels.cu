@@ -255,7 +255,9 @@ __device__ __forceinline__ void persistent_body(const LaunchParams& p) {
                 }
                 // ---- trial pose: cost (model.py:428-462) and, if accepted, the next linearisation
                 hist_slices(p, qi, sh.hist_len, c);
-                evaluate_grad(c, sh.Rn, sh.tn, sh, rp, can_light);
+                // (light only while the previous evaluation found nearly every record in place)
+                evaluate_grad(c, sh.Rn, sh.tn, sh, rp,
+                              can_light && (it == 0 || (long long)sh.ev_ngath * p.light_miss_den <= (long long)sh.ev_nsup));
                 __syncthreads();
                 if (sh.ev_nsup == 0) {  // model.py:441-445 -> CURRENT pose
                     if (tid == 0) {
@@ -829,8 +831,12 @@ __device__ __forceinline__ void task_body(const LaunchParams& p) {
             }
             // light: a trial evaluation, or the first evaluation of the only level right after an inlier pass that left
             // its records (every tag matches) -- records are reused and nearly all of them are in place
+            // ... as far as the evaluation that has just been completed can tell: one that re-used records and still had
+            // to gather more than 1 / light_miss_den of its points says the query is moving across cells, and then the
+            // next evaluation is better cut into tasks again (its rows streamed by several CTAs)
+            const bool few_misses = phase != kPhaseTrial || (long long)sh.ev_ngath * p.light_miss_den <= (long long)sh.ev_nsup;
             const bool light = MODE == kModeRefine && p.light != 0 && p.reuse != 0 &&
-                               (nd_phase == kPhaseTrial ||
+                               ((nd_phase == kPhaseTrial && few_misses) ||
                                 (nd_phase == kPhaseFirst && phase == kPhaseInliers && p.n_levels == 0));
             if (!light) {
                 if (tid == 0) {

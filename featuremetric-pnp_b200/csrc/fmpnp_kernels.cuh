@@ -13,6 +13,10 @@ constexpr int kThreads = kWarps * 32;             // 256
 constexpr int kRecDoubles = 8;                    // per-point record: c, Sxx, Sxy, Syy, bx, by, reuse tag (+1 pad) = 64 B
 constexpr int kRecTagSlot = 6;                    // the record's tag: (generation << 32 | cell) it was gathered for
 constexpr int kRanges = 128;                      // max fixed reduction ranges per query == max tasks per evaluation
+#ifndef FMPNP_RANGE_POINTS
+#define FMPNP_RANGE_POINTS 128
+#endif
+constexpr int kRangePoints = FMPNP_RANGE_POINTS;  // points a fixed reduction range aims at (one transposition + lane tree per range)
 constexpr int kMinRanges = 16;                    // min (small queries) == max cluster size
 constexpr int kMaxCluster = 16;                   // CTAs of a thread-block cluster (non-portable size)
 constexpr int kLaneStride = 34;                   // reduction scratch: doubles per transposed row (16-byte aligned rows, conflict-free 128-bit reads)
@@ -129,6 +133,7 @@ struct LaunchParams {
     // of the query -- the LM state stays in shared memory, nothing goes through the task queue -- with the latency-
     // oriented light_evaluate(); 0: every evaluation takes the general route.  Same bits either way.
     int32_t light;
+    int32_t light_miss_den;  // ... while the previous evaluation gathered at most 1 / light_miss_den of its points
     int32_t l2_policy;      // 1: gathered rows evict_first, staged records evict_last in L2; 0: no preference
 };
 

@@ -41,10 +41,12 @@ struct RingPos {
 };
 
 // Number of fixed reduction ranges of a query: a function of its point count only (never of the launch), a power
-// of two in [16, 128] such that a range holds about 32 points -- a full warp -- when the query has enough of them.
+// of two in [16, 128] such that a range holds about kRangePoints = 128 points -- four rows of a warp, one transposition
+// and lane tree per range -- when the query has enough of them (measured: 32 / 64 / 128 points per range give cfg2
+// 4.56 / 4.40 / 4.32 ms, cfg3 4.42 / 4.28 / 4.22 ms, one cfg3 query alone 1.20 / 0.86 / 0.75 ms; profiles/r02/).
 __device__ __forceinline__ int ranges_of(int N) {
     int r = kMinRanges;
-    while (r < kRanges && N >= 64 * r) r <<= 1;
+    while (r < kRanges && N >= 2 * kRangePoints * r) r <<= 1;
     return r;
 }
 

@@ -28,9 +28,10 @@ def pytest_collection_modifyitems(config, items):
 
 
 # ----------------------------------------------------------------------------------------------
-# Launch routes.  A single query is refined by a thread-block cluster by default; the task scheduler takes
-# over from 5 queries on.  `route` re-runs a test with the process-wide default context replaced by one that
-# forces the scheduler (FMPNP_UNITS is read when a context is created), so that small cases cover both.
+# Launch routes.  The task scheduler is the default for every batch size; an explicit cluster_size (or
+# FMPNP_SCHEDULER=0) selects one CTA / thread-block cluster per query.  `route` re-runs a test with the process-wide
+# default context replaced by one that fixes the tasks per evaluation (FMPNP_UNITS is read when a context is created),
+# so that small cases cover several task counts as well.
 # ----------------------------------------------------------------------------------------------
 _route_ctx = {}
 
@@ -38,15 +39,20 @@ _route_ctx = {}
 def _scheduler_context(units):
     import fmpnp_b200 as fm
     if units not in _route_ctx:
-        os.environ["FMPNP_UNITS"] = str(units)
+        # "light": the light-evaluation route (csrc/fmpnp_light.cuh) forced on for every batch size -- by default it is
+        # taken only by batches of half an SM count of queries or more with a ratio test
+        # (FMPNP_LIGHT_MISS_DEN=1: and kept on however many points an evaluation has to gather)
+        env = {"FMPNP_LIGHT": "1", "FMPNP_LIGHT_MISS_DEN": "1"} if units == "light" else {"FMPNP_UNITS": str(units)}
+        os.environ.update(env)
         try:
             _route_ctx[units] = fm.Context()
         finally:
-            del os.environ["FMPNP_UNITS"]
+            for k in env:
+                del os.environ[k]
     return _route_ctx[units]
 
 
-@pytest.fixture(params=["auto", "tasks2", "tasks128"])
+@pytest.fixture(params=["auto", "tasks2", "tasks128", "light"])
 def route(request):
     if request.param == "auto":
         yield request.param
@@ -56,7 +62,7 @@ def route(request):
     dev = torch.cuda.current_device()
     binding.default_context()
     saved = binding._default_ctx[dev]
-    binding._default_ctx[dev] = _scheduler_context(int(request.param[5:]))
+    binding._default_ctx[dev] = _scheduler_context("light" if request.param == "light" else int(request.param[5:]))
     try:
         yield request.param
     finally:

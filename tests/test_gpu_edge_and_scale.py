@@ -539,3 +539,30 @@ def test_two_contexts_on_two_streams_at_once():
     assert not errs, errs
     for j in range(2):
         assert out[j] is not None and same_records(out[j], solo[j]), "batch %d differs when run concurrently" % j
+
+
+@pytest.mark.parametrize("cfg", ["gn_ratio_inlier", "lm_geman", "pyramid_ratio"])
+def test_light_route_equals_task_route_with_many_misses(cfg):
+    """The light-evaluation route (csrc/fmpnp_light.cuh: one CTA runs a whole evaluation, projection and per-point
+    phase per warp, misses streamed from a per-warp list) against the task route, on queries whose points DO change
+    cell (per-pixel gradients, 1-3 degree errors: more than 32 misses per warp and evaluation, so the list overflows
+    and is flushed in mid-loop), ragged point counts, with history: every record, counter and history entry identical."""
+    from conftest import _scheduler_context
+    s = synth()
+    Ks = ((400.0, 0.0, 255.5), (0.0, 400.0, 254.3), (0.0, 0.0, 1.0))
+    scs = [s.make_scene(4200 + i, N=n, C=128, Hf=64, Wf=64, im_width=512, im_height=512, K=Ks, grad_scale=1.0 / 64,
+                        rot_deg=(1.0, 3.0), outlier_frac=0.1) for i, n in enumerate((2048, 1500, 4096, 777))]
+    probs = [to_problem(sc) for sc in scs]
+    kw = {"gn_ratio_inlier": dict(loss="squared_loss", lambda_=0.0, ratio_threshold=0.8, inlier_threshold=0.8),
+          "lm_geman": dict(loss="geman_mcclure_loss", lambda_=0.01),
+          "pyramid_ratio": dict(loss="huber_loss", lambda_=0.01, ratio_threshold=0.9, levels=[(64, 128), (16, 64), (0, 16)])}[cfg]
+    track = cfg != "gn_ratio_inlier"
+    a = fm().refine_batch(probs, 12, track=track, **kw)
+    b = fm().refine_batch(probs, 12, track=track, ctx=_scheduler_context("light"), **kw)
+    for f in a["results"].dtype.names:
+        assert a["results"][f].tobytes() == b["results"][f].tobytes(), "field %s differs on the light route" % f
+    assert int(a["results"]["gathered_rows"].min()) > 0 and float(a["results"]["reused_rows"].sum()) > 0
+    if track:
+        for k in ("len", "costs", "Rs", "ts", "points2d", "mask", "kept"):
+            assert np.array_equal(a["history"][k], b["history"][k], equal_nan=True) if a["history"][k].dtype.kind == "f" \
+                else np.array_equal(a["history"][k], b["history"][k]), "history %s differs on the light route" % k
