@@ -601,7 +601,11 @@ def main():
     achieved = gath_bytes / (k_ms / 1e3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
+    # the ncu capture was taken on the default workload: it says nothing about another one
+    captured = (args.config == "gn_inlier" and args.queries == 256 and args.points == 4096 and args.channels == 1024 and
+                args.map == 128 and cfg["n_iters"] == 20 and args.grad_scale == 1.0 and list(args.rot_deg) == [0.2, 1.0] and
+                not args.two_calls)
+    if os.path.exists(tpath) and captured:
         try:
             traffic = json.load(open(tpath)).get("refine_kernel_dram_bytes_per_launch_every_row" if args.gather_every_row
                                                  else "refine_kernel_dram_bytes_per_launch")
