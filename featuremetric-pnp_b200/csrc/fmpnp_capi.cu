@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 
 #include "fmpnp_kernels.cuh"
 
@@ -59,6 +60,12 @@ struct fmpnp_ctx {
     int light = -1;  // FMPNP_LIGHT: 1 / 0 = the light evaluations of a launch with record reuse always / never take their own route (fmpnp_light.cuh); -1 = automatic
     // One workspace per context: a call issued on another stream than the previous one waits for that call's
     // kernels first (cudaStreamWaitEvent), so that two launches of a context never overlap on the device.
+    // fmpnp_options.keep_records: what the previous refinement launch worked on (valid while nothing else has touched
+    // the workspace since)
+    bool prev_valid = false;
+    int32_t prev_B = 0, prev_n_max = 0;
+    uint32_t prev_base = 0;
+    std::vector<QueryDev> prev_queries;
     cudaEvent_t last_done = nullptr;
     cudaStream_t last_stream = nullptr;
     bool last_pending = false;
@@ -181,6 +188,7 @@ int stage(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, int grid, int32
         ctx->d_supp = nullptr;
         ctx->d_inl = nullptr;
         ctx->cap_points = 0;
+        ctx->prev_valid = false;
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_rec, need * kRecDoubles * sizeof(double)));
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_supp, need));
         FMPNP_CUDA(ctx, cudaMalloc(&ctx->d_inl, need));
@@ -502,7 +510,19 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
     lp.light = lp.reuse && g.cluster == 1 && light_route(ctx, B, lp.use_ratio != 0) ? 1 : 0;
     lp.inlier_on = (o->inlier_threshold == o->inlier_threshold && o->inlier_threshold != 0.0) ? 1 : 0;  // 0 / NaN = off
     lp.inlier_thr = o->inlier_threshold;
-    {  // one generation per (query, level) of this launch; generations are never handed out twice
+    // fmpnp_options.keep_records: the same arrays as the previous refinement launch of this context (checked: pointers,
+    // sizes, batch, record layout) and nothing in between -> that launch's generations again, so its records match
+    const QueryDev* staged_now = ctx->h_queries[ctx->stage_slot ^ 1];  // what stage() has just filled
+    bool keep = o->keep_records != 0 && lp.reuse != 0 && o->n_levels == 0 && g.units > 0 && ctx->prev_valid &&
+                ctx->prev_B == B && ctx->prev_n_max == n_max && (int32_t)ctx->prev_queries.size() == B;
+    for (int32_t b = 0; keep && b < B; ++b) {
+        const QueryDev &x = staged_now[b], &y = ctx->prev_queries[b];
+        keep = x.F == y.F && x.Gx == y.Gx && x.Gy == y.Gy && x.ref == y.ref && x.pts == y.pts && x.N == y.N && x.C == y.C &&
+               x.Hf == y.Hf && x.Wf == y.Wf && x.im_w == y.im_w && x.im_h == y.im_h;
+    }
+    if (keep) {
+        lp.reuse_base = ctx->prev_base;
+    } else {  // one generation per (query, level) of this launch; generations are never handed out twice
         const uint64_t gens = (uint64_t)B * (uint64_t)levels_eff;
         if (ctx->reuse_next + gens >= (1ull << 32)) {
             FMPNP_CUDA(ctx, cudaMemsetAsync(ctx->d_rec, 0, ctx->cap_points * kRecDoubles * sizeof(double), stream));
@@ -511,6 +531,17 @@ int fmpnp_refine_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t B, co
         if (gens >= (1ull << 32) - 1) lp.reuse = 0;
         lp.reuse_base = (uint32_t)ctx->reuse_next;
         ctx->reuse_next += gens;
+    }
+    ctx->prev_valid = lp.reuse != 0 && o->n_levels == 0 && g.units > 0;
+    if (ctx->prev_valid) {
+        ctx->prev_B = B;
+        ctx->prev_n_max = n_max;
+        ctx->prev_base = lp.reuse_base;
+        try {
+            ctx->prev_queries.assign(staged_now, staged_now + B);
+        } catch (...) {
+            ctx->prev_valid = false;
+        }
     }
     if (hist) {
         lp.hist.enabled = 1;
@@ -554,6 +585,7 @@ int fmpnp_compute_cost_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     fill_common(lp, ctx, B, n_max, g);
     rc = prepare_tasks(ctx, B, g, lp, stream);
     if (rc) return rc;
+    ctx->prev_valid = false;  // this launch overwrites records (fmpnp_options.keep_records)
     lp.mode = kModeComputeCost;
     lp.use_ratio = std::isnan(o->ratio_threshold) ? 0 : 1;
     lp.ratio_thr = lp.use_ratio ? o->ratio_threshold : 0.0;
@@ -652,6 +684,7 @@ int fmpnp_find_inliers_batch(fmpnp_ctx* ctx, const fmpnp_problem* probs, int32_t
     fill_common(lp, ctx, B, n_max, g);
     rc = prepare_tasks(ctx, B, g, lp, stream);
     if (rc) return rc;
+    ctx->prev_valid = false;  // this launch overwrites records (fmpnp_options.keep_records)
     lp.mode = kModeFindInliers;
     lp.loss_id = loss_id;
     lp.alpha = barron_alpha;

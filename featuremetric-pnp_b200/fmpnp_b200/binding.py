@@ -34,7 +34,7 @@ class COptions(C.Structure):
                 ("lambda0", C.c_double), ("ratio_threshold", C.c_double), ("n_levels", C.c_int32),
                 ("levels", (C.c_int32 * 2) * MAX_LEVELS), ("solver", C.c_int32), ("cluster_size", C.c_int32),
                 ("gather_every_row", C.c_int32), ("pad_", C.c_int32), ("inlier_threshold", C.c_double),
-                ("reserved", C.c_int32 * 2)]
+                ("keep_records", C.c_int32), ("reserved", C.c_int32)]
 
 
 class CResult(C.Structure):
@@ -328,8 +328,9 @@ def _problem_array(problems):
 
 
 def _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha=None, cluster_size=0,
-             gather_every_row=False, inlier_threshold=None):
+             gather_every_row=False, inlier_threshold=None, keep_records=False):
     o = COptions()
+    o.keep_records = 1 if keep_records else 0
     o.cluster_size = int(cluster_size)
     o.gather_every_row = 1 if gather_every_row else 0
     o.inlier_threshold = 0.0 if inlier_threshold is None else float(inlier_threshold)
@@ -355,8 +356,11 @@ def _stream_ptr():
 
 def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_threshold=None, levels=None,
                  track=False, solver="cholesky", barron_alpha=None, ctx=None, sync=True, out=None, cluster_size=0,
-                 gather_every_row=False, inlier_threshold=None):
+                 gather_every_row=False, inlier_threshold=None, keep_records=False):
     """Batched sparseFeaturePnP.forward (levels=None) / multilevel_optimization (levels=[(s, e), ...]).
+
+    keep_records=True: the same problems (arrays, sizes, order) as the previous refine_batch call of `ctx`, possibly at
+    other poses: records that call left are reused where they still apply (fmpnp_options.keep_records).
 
     gather_every_row=True reads the rows of every supported point at every evaluation; the default keeps the
     record of a point that stays in its feature-map cell (bit-identical results, see include/fmpnp.h).
@@ -370,7 +374,7 @@ def refine_batch(problems, n_iters, loss="squared_loss", lambda_=0.01, ratio_thr
     B = len(problems)
     dev = torch.device("cuda", ctx.device)
     o = _options(n_iters, loss, lambda_, ratio_threshold, levels, solver, barron_alpha, cluster_size, gather_every_row,
-                 inlier_threshold)
+                 inlier_threshold, keep_records)
     arr = _problem_array(problems)
     res_dev = out if out is not None else torch.empty((max(B, 1), RESULT_DTYPE.itemsize), dtype=torch.uint8, device=dev)
     hist, hbuf = None, None

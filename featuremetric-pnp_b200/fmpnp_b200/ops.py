@@ -12,7 +12,7 @@ kernel behind them.
       K, R0, t0 : (B, 3, 3), (B, 3, 3), (B, 3) float64 CPU tensors
       im_size   : (B, 2) int32 CPU tensor (im_width, im_height)
       opts_f64  : (6,) float64 CPU tensor [n_iters, loss_id, barron_alpha, lambda_, ratio_threshold (nan = None), solver],
-                  optionally followed by [inlier_threshold (0 / nan = off), gather_every_row (0 / 1)]
+                  optionally followed by [inlier_threshold (0 / nan = off), gather_every_row (0 / 1), keep_records (0 / 1)]
       levels    : (L, 2) int32 CPU tensor of channel slices (L = 0: plain forward)
       track     : bool; True also returns the per-iteration history (the reference's track_)
       active    : [] or one (N,) uint8 CUDA mask per query: points with 0 are left out (== pts3D[inliers])
@@ -47,7 +47,8 @@ def refine_batch(F: List[torch.Tensor], Gx: List[torch.Tensor], Gy: List[torch.T
     inl = o[6] if len(o) > 6 and o[6] == o[6] and o[6] != 0.0 else None
     out = _b.refine_batch(probs, int(o[0]), loss=loss, lambda_=o[3], ratio_threshold=rt, levels=lv,
                           solver=int(o[5]), barron_alpha=o[2] if loss == "barron_loss" else None, sync=False,
-                          track=track, inlier_threshold=inl, gather_every_row=len(o) > 7 and o[7] != 0.0)
+                          track=track, inlier_threshold=inl, gather_every_row=len(o) > 7 and o[7] != 0.0,
+                          keep_records=len(o) > 8 and o[8] != 0.0)
     res = [out["results_dev"][: len(probs)].clone()]
     if track:
         h = out["history_dev"]

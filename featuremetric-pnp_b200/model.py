@@ -158,17 +158,19 @@ class sparseFeaturePnP(nn.Module):
         self.track_["threshold_mask"].append(threshold_mask)
 
     # -- shared tail of forward / multilevel_optimization ---------------------------------------
-    def _run(self, prob, levels, track, select=None, inlier_threshold=None):
+    def _run(self, prob, levels, track, select=None, inlier_threshold=None, keep_records=False):
         """One query through torch.ops.fmpnp.refine_batch (PyTorch custom op -> C ABI -> CUDA kernel).
         `select`: boolean mask over the points; the history is reported for those points only (a
         caller that passes pts3D[inliers] to the reference sees exactly these rows).
         `inlier_threshold`: the launch starts with find_inliers(threshold, loss_fn=self.loss_fn) at the initial
-        pose and refines the points it keeps (fmpnp_options.inlier_threshold)."""
+        pose and refines the points it keeps (fmpnp_options.inlier_threshold).
+        `keep_records`: the same arrays as the previous call, possibly at another pose (fmpnp_options.keep_records)."""
         loss_id, alpha = _fm.loss_id_of(self.loss_fn)
         rt = float("nan") if self.ratio_threshold_ is None else float(self.ratio_threshold_)
         solver = {"cholesky": 0, "lu": 1}[self.solver]
         opts = torch.tensor([float(self.iterations), float(loss_id), alpha, float(self.lambda_), rt, float(solver),
-                             0.0 if inlier_threshold is None else float(inlier_threshold), 0.0], dtype=torch.float64)
+                             0.0 if inlier_threshold is None else float(inlier_threshold), 0.0,
+                             1.0 if keep_records else 0.0], dtype=torch.float64)
         lv = torch.tensor(levels if levels else [], dtype=torch.int32).reshape(-1, 2)
         outs = torch.ops.fmpnp.refine_batch(
             [prob.F], [prob.Gx], [prob.Gy], [prob.ref], [prob.pts3D], torch.from_numpy(prob.K.reshape(1, 3, 3)),
@@ -195,6 +197,7 @@ class sparseFeaturePnP(nn.Module):
             self.best_cost_ = torch.tensor(float(r["best_cost"]), dtype=torch.float64)
             self.best_num_inliers_ = int(r["best_num_inliers"])
         self.last_status_ = int(r["status"])
+        self.last_gathered_rows_, self.last_reused_rows_ = int(r["gathered_rows"]), int(r["reused_rows"])
         R = torch.from_numpy(np.array(r["R"], dtype=np.float64).reshape(3, 3).copy())
         t = torch.from_numpy(np.array(r["t"], dtype=np.float64).copy())
         return R, t, r
@@ -269,13 +272,27 @@ class sparseFeaturePnP(nn.Module):
         self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
         return R, t
 
-    def forward_packed(self, prob, track=False, select=None, inlier_threshold=None):
+    def forward_packed(self, prob, track=False, select=None, inlier_threshold=None, keep_records=False):
         """forward() on device-resident inputs (an fmpnp_b200.Problem); with `inlier_threshold`, on the points
         find_inliers(threshold, loss_fn=self.loss_fn) keeps at the initial pose (same launch)."""
-        R_out, t_out, r = self._run(prob, None, track, select, inlier_threshold)
+        R_out, t_out, r = self._run(prob, None, track, select, inlier_threshold, keep_records)
         if self.initial_cost_ is None and int(r["best_num_inliers"]) >= 0:
             self.initial_cost_ = torch.tensor(float(r["initial_cost"]), dtype=torch.float64)
         return R_out, t_out
+
+    def forward_many(self, probs, inlier_threshold=None, levels=None):
+        """forward() / multilevel_optimization (levels = channel slices) of MANY queries in one launch: `probs` is a list
+        of fmpnp_b200.Problem (device-resident inputs, e.g. from pose_prediction.optimize_feature_pnp.build_problem).
+        Not in the reference, whose API is one query per call: called one at a time a query costs 1.4-1.8 ms (launch
+        latency: a single query cannot fill the GPU), in batches of 256 it costs 17 us.  Returns a list of (R, t) CPU
+        float64 tensors and leaves the records (numpy, fmpnp_b200.binding.RESULT_DTYPE) in self.last_results_."""
+        out = _fm.refine_batch(probs, int(self.iterations), loss=self.loss_fn, lambda_=float(self.lambda_),
+                               ratio_threshold=self.ratio_threshold_, solver=self.solver,
+                               levels=[(int(s), int(e)) for s, e in levels] if levels else None,
+                               inlier_threshold=inlier_threshold)
+        self.last_results_ = out["results"]
+        return [(torch.from_numpy(np.array(r["R"], dtype=np.float64).reshape(3, 3).copy()),
+                 torch.from_numpy(np.array(r["t"], dtype=np.float64).copy())) for r in out["results"]]
 
     def compute_cost(self, pts3D, R, t, feature_map_query, feature_ref, K, im_width, im_height):
         """Mean of 0.5 * ||F[cell] - ref||^2 over the supported points (after the raw-SSD ratio

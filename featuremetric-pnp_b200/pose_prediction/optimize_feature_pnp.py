@@ -127,13 +127,19 @@ def feature_pnp_multi(query_hypercolumns, reference_hypercolumns, prediction, K,
         print("No initial inliers found.")
         inliers = None  # selected at (R, t) by the first round
     model = sparseFeaturePnP()  # parameters from gin
+    fused_before = False  # the previous round was such a launch on these very arrays: its records still apply
     for _ in range(3):
         if inliers is None:
             thr, loss = selection_args()
             if not track and _fm.loss_id_of(loss) == _fm.loss_id_of(model.loss_fn):
-                R, t = model.forward_packed(_with(prob, R, t), inlier_threshold=thr)  # selection + refinement, one launch
+                # selection + refinement, one launch; from the second such round on the launch starts from the records
+                # the previous one left (fmpnp_options.keep_records): a point that is still in the cell it was last
+                # gathered for -- nearly all of them, the round starts where the previous one ended -- reads nothing
+                R, t = model.forward_packed(_with(prob, R, t), inlier_threshold=thr, keep_records=fused_before)
+                fused_before = True
                 continue
             inliers = select(R, t)
+        fused_before = False
         R, t = model.forward_packed(_with(prob, R, t, active=inliers), track=track,
                                     select=inliers.bool().cpu().numpy() if track else None)
         inliers = None  # re-selected at the refined pose by the next round

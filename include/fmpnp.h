@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define FMPNP_VERSION 102
+#define FMPNP_VERSION 103
 #define FMPNP_MAX_LEVELS 8
 
 typedef struct fmpnp_ctx fmpnp_ctx;
@@ -129,7 +129,16 @@ typedef struct {
                                results as fmpnp_find_inliers_batch followed by fmpnp_refine_batch with its mask as
                                `active`; without a pyramid the pass's records serve the first evaluation, so the
                                rows are gathered once instead of twice */
-    int32_t reserved[2];
+    int32_t keep_records;     /* 0 (default): nothing carries over from one call to the next.  1: this call refines the SAME
+                               problems as the previous fmpnp_refine_batch call of this context -- same F / Gx / Gy / ref /
+                               pts3D arrays with unchanged contents, same sizes, same order; poses, K and masks may differ --
+                               so the records that call left may be reused where a point still projects into the cell it
+                               was last gathered for: rounds 2 and 3 of feature_pnp_multi (optimize_feature_pnp.py:20-47)
+                               start where round 1 ended and gather next to nothing.  Single level only (n_levels == 0),
+                               record reuse on, task scheduler; ignored (a normal call) when the pointers, sizes or batch
+                               differ from the previous call's, or when any other call of the context came in between.
+                               Results are bit-identical either way; only gathered_rows / reused_rows differ. */
+    int32_t reserved;
 } fmpnp_options;
 
 /* What the callers read back (sparse_to_dense_predictor.py:257): the returned pose,

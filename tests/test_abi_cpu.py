@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
     L = ctypes.CDLL(fm.lib_path())
     for n in names:
         assert hasattr(L, n), "libfmpnp.so does not export " + n
-    assert fm.lib().fmpnp_version() == 102
+    assert fm.lib().fmpnp_version() == 103
 
 
 def test_struct_sizes_match_the_c_abi():
@@ -104,7 +104,7 @@ def test_header_is_plain_c_and_links_against_the_library(tmp_path):
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
                     str(src), "-o", str(exe), "-L", libdir, "-lfmpnp", "-Wl,-rpath," + libdir], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
-    assert int(out[0]) == 102 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)
+    assert int(out[0]) == 103 and int(out[1]) == int(out[4]) and int(out[5]) == len(names)
     # the ctypes mirrors place the fields added in version 101 where the C compiler does
     from fmpnp_b200 import binding as b
     import ctypes

@@ -566,3 +566,44 @@ def test_light_route_equals_task_route_with_many_misses(cfg):
         for k in ("len", "costs", "Rs", "ts", "points2d", "mask", "kept"):
             assert np.array_equal(a["history"][k], b["history"][k], equal_nan=True) if a["history"][k].dtype.kind == "f" \
                 else np.array_equal(a["history"][k], b["history"][k]), "history %s differs on the light route" % k
+
+
+def test_keep_records_starts_from_the_previous_launch():
+    """fmpnp_options.keep_records: a second launch on the same arrays (other poses) reuses the records the first one
+    left -- same results as without, next to nothing gathered; any other call on the context in between, or other
+    arrays, makes it a normal call."""
+    s = synth()
+    Ks = ((400.0, 0.0, 255.5), (0.0, 400.0, 254.3), (0.0, 0.0, 1.0))
+    scs = [s.make_scene(5100 + i, N=n, C=256, Hf=64, Wf=64, im_width=512, im_height=512, K=Ks, outlier_frac=0.1)
+           for i, n in enumerate((1500, 2048, 900))]
+    first = [to_problem(sc) for sc in scs]
+    kw = dict(loss="squared_loss", lambda_=0.0, ratio_threshold=0.8, inlier_threshold=0.8)
+    ca, cb = fm().Context(), fm().Context()
+    r1a = fm().refine_batch(first, 6, ctx=ca, **kw)["results"]
+    r1b = fm().refine_batch(first, 6, ctx=cb, **kw)["results"]
+    assert same_records(r1a, r1b)
+
+    def again(res):  # round 2 of feature_pnp_multi: the same arrays at the pose round 1 returned
+        return [fm().Problem(p.F, p.Gx, p.Gy, p.ref, p.pts3D, p.K, np.array(r["R"]), np.array(r["t"]), p.im_width, p.im_height)
+                for p, r in zip(first, res)]
+
+    second = again(r1a)
+    r2a = fm().refine_batch(second, 6, ctx=ca, keep_records=True, **kw)["results"]
+    r2b = fm().refine_batch(second, 6, ctx=cb, **kw)["results"]
+    counters = ("gathered_rows", "reused_rows")
+    assert same_records(r2a, r2b, skip=counters)
+    assert np.array_equal(r2a["gathered_rows"] + r2a["reused_rows"], r2b["gathered_rows"] + r2b["reused_rows"])
+    assert r2a["gathered_rows"].sum() < 0.1 * r2b["gathered_rows"].sum(), (r2a["gathered_rows"], r2b["gathered_rows"])
+    # another call of the context in between: its records are gone, the option is ignored
+    fm().compute_cost_batch(second, ctx=ca)
+    r3a = fm().refine_batch(second, 6, ctx=ca, keep_records=True, **kw)["results"]
+    assert same_records(r3a, r2b)
+    # other arrays (copies): ignored as well
+    r4a = fm().refine_batch(second, 6, ctx=ca, keep_records=True, **kw)["results"]  # (this one does reuse: same arrays again)
+    assert same_records(r4a, r2b, skip=counters) and r4a["gathered_rows"].sum() < 0.1 * r2b["gathered_rows"].sum()
+    copies = [fm().Problem(p.F.clone(), p.Gx.clone(), p.Gy.clone(), p.ref.clone(), p.pts3D.clone(), p.K, p.R0, p.t0,
+                           p.im_width, p.im_height) for p in second]
+    r5a = fm().refine_batch(copies, 6, ctx=ca, keep_records=True, **kw)["results"]
+    assert same_records(r5a, r2b)
+    ca.close()
+    cb.close()

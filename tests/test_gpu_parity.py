@@ -140,3 +140,24 @@ def test_find_inliers_and_compute_cost():
                          torch.from_numpy(chw64(g["F"])), torch.from_numpy(g["ref"]).double(), torch.from_numpy(g["K"]),
                          g["im_width"], g["im_height"])
     assert abs(c3.item() - float(g["compute_cost_ratio07"])) <= TIGHT * float(g["compute_cost_ratio07"])
+
+
+def test_forward_many_equals_forward_packed_per_query():
+    """model.sparseFeaturePnP.forward_many: a list of device-resident problems in one launch gives, query by query, what
+    forward_packed / multilevel_packed return one at a time (same records: the reduction order is fixed)."""
+    import helpers.utils as hu
+    import model
+    import fmpnp_b200 as fm
+    from fmpnp_b200 import synth
+    Ks = ((400.0, 0.0, 255.5), (0.0, 400.0, 254.3), (0.0, 0.0, 1.0))
+    scs = [synth.make_scene(7300 + i, N=n, C=64, Hf=32, Wf=32, im_width=512, im_height=512, K=Ks, grad_scale=1.0 / 64,
+                            outlier_frac=0.1) for i, n in enumerate((700, 1024, 333, 2000))]
+    probs = [fm.Problem(sc.F.cuda(), sc.Gx.cuda(), sc.Gy.cuda(), sc.ref.cuda(), sc.pts3D.cuda(), sc.K, sc.R0, sc.t0,
+                        sc.im_width, sc.im_height) for sc in scs]
+    m = model.sparseFeaturePnP(n_iters=10, loss_fn=hu.geman_mcclure_loss, lambda_=0.01, ratio_threshold=None)
+    for levels in (None, [(32, 64), (0, 32)]):
+        many = m.forward_many(probs, levels=levels)
+        assert len(many) == len(probs) and m.last_results_.shape == (len(probs),)
+        for p, (R, t) in zip(probs, many):
+            R1, t1 = m.forward_packed(p) if levels is None else m.multilevel_packed(levels, p)
+            assert R.dtype == torch.float64 and torch.equal(R, R1) and torch.equal(t, t1)

@@ -21,6 +21,18 @@ for C, levels in ((1024, [(512, 1024), (128, 512), (0, 128)]), (20, [(8, 20), (0
         r = fm.refine_batch([p] * (3 if S == 1 else 1), 3, loss="geman_mcclure_loss", lambda_=0.01, ratio_threshold=0.9,
                             levels=levels, track=True, cluster_size=S)["results"]
         assert int(r["status"][0]) == 0
+    # task scheduler (default route), and the light-evaluation route forced on (FMPNP_LIGHT is read when a context is made)
+    r = fm.refine_batch([p] * 5, 3, loss="squared_loss", lambda_=0.0, ratio_threshold=0.8, inlier_threshold=0.8 if levels is None else None,
+                        levels=levels)["results"]
+    assert int(r["status"][0]) >= 0
+    os.environ["FMPNP_LIGHT"] = "1"
+    os.environ["FMPNP_LIGHT_MISS_DEN"] = "1"
+    lctx = fm.Context()
+    del os.environ["FMPNP_LIGHT"], os.environ["FMPNP_LIGHT_MISS_DEN"]
+    r2 = fm.refine_batch([p] * 5, 3, loss="squared_loss", lambda_=0.0, ratio_threshold=0.8, inlier_threshold=0.8 if levels is None else None,
+                         levels=levels, ctx=lctx)["results"]
+    assert r2["R"].tobytes() == r["R"].tobytes()
+    lctx.close()
     fm.find_inliers_batch([p, p], 0.8, loss="cauchy_loss")
     fm.compute_cost_batch([p], ratio_threshold=0.7)
 x = torch.rand((37, 19, 23), device=dev)
