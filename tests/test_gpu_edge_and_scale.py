@@ -561,6 +561,10 @@ def test_light_route_equals_task_route_with_many_misses(cfg):
     b = fm().refine_batch(probs, 12, track=track, ctx=_scheduler_context("light"), **kw)
     for f in a["results"].dtype.names:
         assert a["results"][f].tobytes() == b["results"][f].tobytes(), "field %s differs on the light route" % f
+    # the same route of the one-CTA-per-query kernel (cluster_size = 1: fmpnp::refine_kernel runs light_evaluate too)
+    b1 = fm().refine_batch(probs, 12, track=track, ctx=_scheduler_context("light"), cluster_size=1, **kw)
+    for f in a["results"].dtype.names:
+        assert a["results"][f].tobytes() == b1["results"][f].tobytes(), "field %s differs on the per-query light route" % f
     assert int(a["results"]["gathered_rows"].min()) > 0 and float(a["results"]["reused_rows"].sum()) > 0
     if track:
         for k in ("len", "costs", "Rs", "ts", "points2d", "mask", "kept"):
