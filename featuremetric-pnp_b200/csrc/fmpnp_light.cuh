@@ -6,9 +6,9 @@
 // records, the same per-point phase (reduce_points) -- but organised for latency instead of bandwidth:
 //   * a warp works on the points of the reduction ranges it owns, in both phases, so nothing but the ratio-test limit
 //     crosses warps: one block barrier per evaluation (none without a ratio test) instead of three;
-//   * the projection runs over four points per lane at a time with all their loads (point, tag, first record entry,
-//     mask) issued together: one L2 round trip per 128 points of a warp instead of one per 32, and four independent
-//     float64 division chains in flight per thread;
+//   * the projection runs over two points per lane at a time (two independent pairs of float64 division chains per
+//     thread), and what it reads of them -- coordinates, tag, first record entry -- is staged into the warp's ring
+//     slice with cp.async one group AHEAD: the L2 round trip is behind the arithmetic, no register holds data in flight;
 //   * the ratio-test maximum is taken from the records on the way (the first entry of a record shares the tag's
 //     cache line), not in a pass of its own;
 //   * the few points that left their cell are listed per warp and streamed by that warp through its slice of the ring
